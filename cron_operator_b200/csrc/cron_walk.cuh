@@ -1,0 +1,398 @@
+// cron_walk.cuh -- per-spec schedule walk shared by every kernel in this library.
+//
+// What it computes: (*SpecSchedule).Next(t) of robfig/cron v3.0.1 (spec.go; called from the reference at
+// internal/controller/cron_controller.go:405,409,436) with Go `time` semantics (Date's two-lookup zone resolution,
+// absolute Add, AddDate through Date, the day loop's "hour != 0" DST fix, the 5-year limit).
+//
+// How: the reference walks month/day/hour/minute/second loops one unit at a time, re-deriving civil fields from
+// absolute time at every step (58 steps for "* * * * *", 206 for an unschedulable spec).  Here the walk keeps its
+// civil fields resident in registers (local day number, second of day, Y/M/D, current zone period) and every loop
+// *jumps* with a bit scan over the mask when the whole jump provably lies inside one constant-offset period of the
+// zone -- in which case the unit steps it replaces are uniform and the end state is identical.  When a jump would
+// touch a zone transition (or a Date() target that is not "natural"), the walk falls back to one literal upstream
+// step and tries again, so DST gaps/overlaps, midnight-gap zones and 30-minute shifts reproduce upstream's
+// behaviour step for step.  UTC is the degenerate zone with one infinite period: every jump is taken.
+//
+// One lane walks one spec ("warp-cooperative" in this library means the loads and the output staging, see
+// next_kernels.cu); nothing here is a contraction, so no tensor cores.
+#pragma once
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define CW_HD __host__ __device__ __forceinline__
+#define CW_LDG(p) __ldg(p)
+#else
+#define CW_HD inline
+#define CW_LDG(p) (*(p))
+#endif
+
+namespace cronwalk {
+
+constexpr int64_t kZero = INT64_MIN;  // Go's time.Time{} at every boundary of this library
+constexpr int64_t kAlpha = INT64_MIN;
+constexpr int64_t kOmega = INT64_MAX;
+
+// Flattened zone table in HBM (L2-resident: ~0.5 MB for all IANA zones).  Zone z owns entries
+// [zstart[z], zstart[z+1]); entry i is in force for when[i] <= sec < when[i+1] (when of the first entry is kAlpha,
+// the last period is open-ended).  Footer rules are pre-expanded to explicit entries up to `horizon`.
+struct ZoneTable {
+  const int64_t* when;
+  const int32_t* off;
+  const int32_t* zstart;
+  int32_t nzones;
+  int64_t horizon;  // zoned inputs must be < horizon - 6 years (checked by the caller of the kernels)
+};
+
+struct Spec {  // sanitised masks: only the bits upstream can test are kept
+  uint64_t second, minute;
+  uint32_t hour, dom, month, dow;
+  bool star;   // Dom&starBit || Dow&starBit  -> AND rule, else OR rule (spec.go dayMatches)
+  bool never;  // some field can never match: upstream walks to the 5-year limit and returns the zero time
+};
+
+CW_HD Spec make_spec(uint64_t second, uint64_t minute, uint64_t hour, uint64_t dom, uint64_t month, uint64_t dow) {
+  Spec s;
+  s.second = second & ((1ULL << 60) - 1);
+  s.minute = minute & ((1ULL << 60) - 1);
+  s.hour = (uint32_t)(hour & 0xFFFFFFu);
+  s.dom = (uint32_t)(dom & 0xFFFFFFFEu);
+  s.month = (uint32_t)(month & 0x1FFEu);
+  s.dow = (uint32_t)(dow & 0x7Fu);
+  s.star = ((dom | dow) >> 63) != 0;
+  const bool no_day = s.star ? (s.dom == 0 || s.dow == 0) : (s.dom == 0 && s.dow == 0);
+  s.never = s.second == 0 || s.minute == 0 || s.hour == 0 || s.month == 0 || no_day;
+  return s;
+}
+
+// ---- small integer helpers --------------------------------------------------------------------------------
+CW_HD int ctz32(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+  return __ffs((int)x) - 1;
+#else
+  return __builtin_ctz(x);
+#endif
+}
+CW_HD int ctz64(uint64_t x) {
+#if defined(__CUDA_ARCH__)
+  return __ffsll((long long)x) - 1;
+#else
+  return __builtin_ctzll(x);
+#endif
+}
+CW_HD int popc32(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+  return __popc(x);
+#else
+  return __builtin_popcount(x);
+#endif
+}
+CW_HD int popc64(uint64_t x) {
+#if defined(__CUDA_ARCH__)
+  return __popcll(x);
+#else
+  return __builtin_popcountll(x);
+#endif
+}
+CW_HD int clz32(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+  return __clz((int)x);
+#else
+  return x ? __builtin_clz(x) : 32;
+#endif
+}
+CW_HD int clz64(uint64_t x) {
+#if defined(__CUDA_ARCH__)
+  return __clzll((long long)x);
+#else
+  return x ? __builtin_clzll(x) : 64;
+#endif
+}
+
+CW_HD int32_t days_from_civil(int32_t y, int32_t m, int32_t d) {  // proleptic Gregorian, 1970-01-01 = 0
+  y -= m <= 2;
+  const int32_t era = (y >= 0 ? y : y - 399) / 400;
+  const uint32_t yoe = (uint32_t)(y - era * 400);
+  const uint32_t doy = (153u * (uint32_t)(m > 2 ? m - 3 : m + 9) + 2u) / 5u + (uint32_t)d - 1u;
+  const uint32_t doe = yoe * 365u + yoe / 4u - yoe / 100u + doy;
+  return era * 146097 + (int32_t)doe - 719468;
+}
+CW_HD void civil_from_days(int32_t z, int32_t& y, int32_t& m, int32_t& d) {
+  z += 719468;
+  const int32_t era = (z >= 0 ? z : z - 146096) / 146097;
+  const uint32_t doe = (uint32_t)(z - era * 146097);
+  const uint32_t yoe = (doe - doe / 1460u + doe / 36524u - doe / 146096u) / 365u;
+  const uint32_t doy = doe - (365u * yoe + yoe / 4u - yoe / 100u);
+  const uint32_t mp = (5u * doy + 2u) / 153u;
+  d = (int32_t)(doy - (153u * mp + 2u) / 5u + 1u);
+  m = (int32_t)(mp < 10u ? mp + 3u : mp - 9u);
+  y = (int32_t)yoe + era * 400 + (m <= 2);
+}
+CW_HD bool is_leap(int32_t y) { return (y % 4 == 0) && (y % 100 != 0 || y % 400 == 0); }
+CW_HD int32_t days_in_month(int32_t y, int32_t m) {
+  // 31 for 1,3,5,7,8,10,12; 30 for 4,6,9,11; February by leap rule
+  if (m == 2) return is_leap(y) ? 29 : 28;
+  return 30 + (int32_t)((0x15AAu >> m) & 1u);
+}
+CW_HD int32_t weekday_of(int32_t dn) {  // Sunday = 0; 1970-01-01 was a Thursday
+  int32_t w = (dn + 4) % 7;
+  return w < 0 ? w + 7 : w;
+}
+
+// ---- the walk ------------------------------------------------------------------------------------------------
+struct Walk {
+  // zone
+  const int64_t* zw;   // this zone's `when` entries
+  const int32_t* zo;   // this zone's offsets
+  int32_t zn;          // entry count (1 for UTC / fixed zones)
+  // cached period holding the last looked-up instant
+  int32_t pidx;
+  int32_t off;
+  int64_t ps, pe;
+  // current instant and its civil fields in the zone
+  int64_t t;
+  int32_t dn;   // local day number
+  int32_t sod;  // local second of day
+  int32_t Y, M, D;
+
+  CW_HD void bind_utc() {
+    zw = nullptr; zo = nullptr; zn = 1; pidx = 0; off = 0; ps = kAlpha; pe = kOmega;
+  }
+  CW_HD void bind_zone(const ZoneTable& zt, int32_t zone) {
+    const int32_t a = CW_LDG(zt.zstart + zone), b = CW_LDG(zt.zstart + zone + 1);
+    zw = zt.when + a; zo = zt.off + a; zn = b - a;
+    pidx = -1; off = 0; ps = 1; pe = 0;  // empty cache
+    if (zn == 1) { pidx = 0; off = CW_LDG(zo); ps = kAlpha; pe = kOmega; }
+  }
+
+  // (*Location).lookup(x).offset; moves the cached period to the one containing x
+  CW_HD int32_t lookup(int64_t x) {
+    if (x >= ps && x < pe) return off;
+    int32_t lo = 0, hi = zn;  // largest lo with when[lo] <= x  (when[0] == kAlpha)
+    if (pidx >= 0) {          // transitions are usually crossed one at a time: try the neighbours first
+      if (x >= pe) { lo = pidx + 1; if (lo + 1 >= zn || x < CW_LDG(zw + lo + 1)) hi = lo + 1; }
+      else { hi = pidx; if (hi - 1 >= 0 && x >= CW_LDG(zw + hi - 1)) lo = hi - 1; }
+    }
+    while (hi - lo > 1) {
+      const int32_t mid = (int32_t)((uint32_t)(lo + hi) >> 1);
+      if (x < CW_LDG(zw + mid)) hi = mid; else lo = mid;
+    }
+    pidx = lo;
+    off = CW_LDG(zo + lo);
+    ps = CW_LDG(zw + lo);
+    pe = (lo + 1 < zn) ? CW_LDG(zw + lo + 1) : kOmega;
+    return off;
+  }
+
+  // field getters on the resident state
+  CW_HD int32_t hour() const { return sod / 3600; }
+  CW_HD int32_t minute() const { return (sod % 3600) / 60; }
+  CW_HD int32_t second() const { return sod % 60; }
+
+  // set the current instant and re-derive every field (what Go does on each t.Month()/t.Day()/... call)
+  CW_HD void load(int64_t tt) {
+    t = tt;
+    const int64_t l = tt + lookup(tt);
+    int64_t q = l / 86400;
+    int32_t r = (int32_t)(l - q * 86400);
+    if (r < 0) { r += 86400; q -= 1; }
+    dn = (int32_t)q;
+    sod = r;
+    civil_from_days(dn, Y, M, D);
+  }
+
+  // time.Date(y, mo, d, h, mi, s, 0, loc): as-if-UTC seconds, then the two-lookup offset resolution
+  CW_HD int64_t go_date(int32_t y, int32_t mo, int32_t d, int32_t sod_) {
+    int32_t m0 = mo - 1;
+    if (m0 >= 12) { y += m0 / 12; m0 %= 12; }
+    const int64_t x = (int64_t)(days_from_civil(y, m0 + 1, 1) + (d - 1)) * 86400 + sod_;
+    int32_t o = lookup(x);
+    if (o != 0) o = lookup(x - o);  // Go: keep o when utc stays in [start,end) -- same value either way
+    return x - o;
+  }
+  // Is local wall time x (as-if-UTC seconds) resolved by Date() to x - off with the current period untouched?
+  CW_HD bool natural(int64_t x) const {
+    const int64_t u = x - off;
+    return x >= ps && x < pe && u >= ps && u < pe;
+  }
+
+  // move the resident fields forward by k whole days inside the same period (k >= 1, small)
+  CW_HD void advance_days(int32_t k) {
+    dn += k;
+    D += k;
+    int32_t dim = days_in_month(Y, M);
+    while (D > dim) {
+      D -= dim;
+      if (++M == 13) { M = 1; ++Y; }
+      dim = days_in_month(Y, M);
+    }
+  }
+};
+
+// 31-bit mask of the days of month (Y, M) on which dayMatches() holds; bit d = day d
+CW_HD uint32_t month_daymask(const Spec& s, int32_t Y, int32_t M, int32_t dn_of_first) {
+  const int32_t dim = days_in_month(Y, M);
+  const uint32_t valid = (uint32_t)(((1ULL << (dim + 1)) - 1ULL) & ~1ULL);
+  const int32_t wd1 = weekday_of(dn_of_first);
+  // replicate the 7-bit dow mask so that bit j = dow bit (j mod 7), j < 42; day d has weekday (wd1 + d - 1) mod 7
+  const uint64_t rep = (uint64_t)s.dow * 0x0000000810204081ULL;  // 1 + 2^7 + 2^14 + 2^21 + 2^28 + 2^35
+  const uint32_t dowm = (uint32_t)((rep >> wd1) << 1);
+  const uint32_t m = s.star ? (s.dom & dowm) : (s.dom | dowm);
+  return m & valid;
+}
+
+CW_HD bool day_matches(const Spec& s, int32_t D, int32_t dn) {
+  const bool dom = (s.dom >> D) & 1u;
+  const bool dow = (s.dow >> weekday_of(dn)) & 1u;
+  return s.star ? (dom && dow) : (dom || dow);
+}
+
+// Continue an upstream Next() walk from the resident state `w` (which already holds t = input + 1s).
+// Returns the fire time (w then holds its fields) or kZero.
+CW_HD int64_t walk_next(const Spec& s, Walk& w) {
+  if (s.never) return kZero;
+  bool added = false;
+  const int32_t year_limit = w.Y + 5;
+
+  for (;;) {  // WRAP:
+    if (w.Y > year_limit) return kZero;
+
+    // ---------------- month loop ----------------
+    bool wrapped = false;
+    while (((s.month >> w.M) & 1u) == 0) {
+      if (!added) {
+        added = true;
+        w.load(w.go_date(w.Y, w.M, 1, 0));
+      }
+      // jump: D == 1 means AddDate(0,1,0) lands on the 1st of each following month with h:m:s unchanged
+      const uint32_t later = s.month & ~((2u << w.M) - 1u);
+      const int32_t tgtM = later ? ctz32(later) : 13;  // 13 = January of next year (-> WRAP)
+      bool jumped = false;
+      if (w.D == 1) {
+        const int32_t dn_first = days_from_civil(w.Y, w.M + 1, 1);  // first step
+        const int32_t dn_last = (tgtM == 13) ? days_from_civil(w.Y + 1, 1, 1) : days_from_civil(w.Y, tgtM, 1);
+        if (w.natural((int64_t)dn_first * 86400 + w.sod) && w.natural((int64_t)dn_last * 86400 + w.sod)) {
+          w.t = (int64_t)dn_last * 86400 + w.sod - w.off;
+          w.dn = dn_last;
+          if (tgtM == 13) { w.M = 1; w.Y += 1; } else { w.M = tgtM; }
+          jumped = true;
+        }
+      }
+      if (!jumped) {
+        w.load(w.go_date(w.Y, w.M + 1, w.D, w.sod));  // literal AddDate(0,1,0)
+      }
+      if (w.M == 1) { wrapped = true; break; }
+    }
+    if (wrapped) continue;
+
+    // ---------------- day loop ----------------
+    while (!day_matches(s, w.D, w.dn)) {
+      if (!added) {
+        added = true;
+        w.load(w.go_date(w.Y, w.M, w.D, 0));
+      }
+      bool jumped = false;
+      if (w.sod < 3600) {  // hour == 0: the "hour != 0" fix cannot trigger on natural steps
+        const uint32_t dm = month_daymask(s, w.Y, w.M, w.dn - (w.D - 1));
+        const uint32_t later = dm & ~((2u << w.D) - 1u);
+        const int32_t dim = days_in_month(w.Y, w.M);
+        const int32_t k = (later ? ctz32(later) : dim + 1) - w.D;  // dim+1 = the 1st of next month (-> WRAP)
+        const int64_t x1 = (int64_t)(w.dn + 1) * 86400 + w.sod;
+        const int64_t xk = (int64_t)(w.dn + k) * 86400 + w.sod;
+        if (w.natural(x1) && w.natural(xk)) {
+          w.t = xk - w.off;
+          w.advance_days(k);
+          jumped = true;
+        }
+      }
+      if (!jumped) {
+        w.load(w.go_date(w.Y, w.M, w.D + 1, w.sod));  // literal AddDate(0,0,1)
+        const int32_t h = w.hour();
+        if (h != 0) {  // "Notice if the hour is no longer midnight due to DST."
+          if (h > 12) w.load(w.t + (int64_t)(24 - h) * 3600);
+          else w.load(w.t - (int64_t)h * 3600);
+        }
+      }
+      if (w.D == 1) { wrapped = true; break; }
+    }
+    if (wrapped) continue;
+
+    // ---------------- hour loop ----------------
+    while (((s.hour >> w.hour()) & 1u) == 0) {
+      if (!added) {
+        added = true;
+        w.load(w.go_date(w.Y, w.M, w.D, w.hour() * 3600));
+      }
+      const int32_t h = w.hour();  // after the reset: a Date() inside a gap can move the hour
+      const uint32_t later = s.hour & ~((2u << h) - 1u);
+      const int32_t k = (later ? ctz32(later) : 24) - h;  // 24 = hour 0 of the next day (-> WRAP)
+      const int64_t tk = w.t + (int64_t)k * 3600;
+      if (tk < w.pe) {  // k absolute one-hour steps inside one period: the local hour advances by one each
+        w.t = tk;
+        w.sod += k * 3600;
+        if (w.sod >= 86400) { w.sod -= 86400; w.advance_days(1); }
+      } else {
+        w.load(w.t + 3600);  // literal step across (or up to) the transition
+      }
+      if (w.hour() == 0) { wrapped = true; break; }
+    }
+    if (wrapped) continue;
+
+    // ---------------- minute loop ----------------
+    while (((s.minute >> w.minute()) & 1ULL) == 0) {
+      if (!added) {
+        added = true;
+        // Truncate(time.Minute) works on absolute time; the zero Time is a multiple of 60 s away from 1970
+        int64_t r = w.t % 60;
+        if (r < 0) r += 60;
+        if (r != 0) w.load(w.t - r);
+      }
+      const int32_t mi = w.minute();
+      const uint64_t later = s.minute & ~((2ULL << mi) - 1ULL);
+      const int32_t k = (later ? ctz64(later) : 60) - mi;  // 60 = minute 0 of the next hour (-> WRAP)
+      const int64_t tk = w.t + (int64_t)k * 60;
+      if (tk < w.pe) {
+        w.t = tk;
+        w.sod += k * 60;
+        if (w.sod >= 86400) { w.sod -= 86400; w.advance_days(1); }
+      } else {
+        w.load(w.t + 60);
+      }
+      if (w.minute() == 0) { wrapped = true; break; }
+    }
+    if (wrapped) continue;
+
+    // ---------------- second loop ----------------
+    while (((s.second >> w.second()) & 1ULL) == 0) {
+      added = true;  // Truncate(time.Second) is the identity on whole seconds
+      const int32_t sc = w.second();
+      const uint64_t later = s.second & ~((2ULL << sc) - 1ULL);
+      const int32_t k = (later ? ctz64(later) : 60) - sc;  // 60 = second 0 of the next minute (-> WRAP)
+      const int64_t tk = w.t + k;
+      if (tk < w.pe) {
+        w.t = tk;
+        w.sod += k;
+        if (w.sod >= 86400) { w.sod -= 86400; w.advance_days(1); }
+      } else {
+        w.load(w.t + 1);
+      }
+      if (w.second() == 0) { wrapped = true; break; }
+    }
+    if (wrapped) continue;
+
+    return w.t;
+  }
+}
+
+// Next(t): t.Add(1s) then the walk.  `resident` = w already holds the fields of `t` (chained NextN calls).
+CW_HD int64_t next_from(const Spec& s, Walk& w, int64_t t, bool resident) {
+  const int64_t t1 = t + 1;
+  if (resident && t1 < w.pe && w.sod + 1 < 86400) {
+    w.t = t1;
+    w.sod += 1;
+  } else {
+    w.load(t1);
+  }
+  return walk_next(s, w);
+}
+
+}  // namespace cronwalk

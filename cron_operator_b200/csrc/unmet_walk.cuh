@@ -1,0 +1,213 @@
+// unmet_walk.cuh -- per-spec missed-run enumeration + concurrency decision.
+//
+// Replaces getNextSchedule (internal/controller/cron_controller.go:389-437) and the gates + Allow/Forbid/Replace
+// decision of Reconcile (:163-220) for one Cron.  The reference chains sched.Next() once per missed run (43,200
+// calls for "* * * * *" over a 30-day backlog); here the chain is only walked call by call where a zone transition
+// can perturb it, and stretches inside one constant-offset period are counted with popcounts (chain_fast_forward).
+#pragma once
+#include "cron_walk.cuh"
+#include <limits.h>
+
+namespace cronwalk {
+
+enum : uint8_t { kStOk = 0, kStUnschedulable = 1, kStEarliestAfterNow = 2 };
+enum : uint8_t {
+  kDecGateDeleted = 1,       // cron_controller.go:163-166
+  kDecGateSuspended = 2,     // :169-173
+  kDecGateDeadline = 3,      // :176-180
+  kDecErrUnschedulable = 4,  // :185-190  ("unschedulable cron" error: no requeue)
+  kDecRequeueOnly = 5,       // :196-199  (no missed run)
+  kDecSkipForbid = 6,        // :204-207
+  kDecReplaceCreate = 7,     // :210-220 then :222-238
+  kDecCreate = 8             // :222-238
+};
+enum : uint8_t { kPolicyAllow = 0, kPolicyForbid = 1, kPolicyReplace = 2 };
+enum : uint8_t { kFlagSuspend = 1, kFlagDeleted = 2 };
+
+struct UnmetIn {
+  int64_t earliest;  // Status.LastScheduleTime ?: CreationTimestamp  (:397-402)
+  int64_t now;       // floor(now) in unix seconds
+  int32_t now_nsec;  // sub-second part of now; only the deadline gate can observe it
+  uint8_t policy, flags;
+  uint32_t active;
+  int64_t deadline;  // kZero == Spec.Deadline is nil
+};
+struct UnmetOut {
+  int64_t last, next;
+  uint32_t missed;  // saturates at 0xffffffff
+  uint8_t status, decision;
+};
+
+CW_HD uint32_t sat_add(uint32_t a, uint64_t b) {
+  const uint64_t r = (uint64_t)a + b;
+  return r > 0xffffffffULL ? 0xffffffffu : (uint32_t)r;
+}
+
+// number of matching times of day with second-of-day <= sod (sod in [0, 86399])
+CW_HD uint32_t count_tod_le(const Spec& s, int32_t sod) {
+  const int32_t h = sod / 3600, mi = (sod % 3600) / 60, sc = sod % 60;
+  const uint32_t pm = (uint32_t)popc64(s.minute), psec = (uint32_t)popc64(s.second);
+  uint32_t c = (uint32_t)popc32(s.hour & ((1u << h) - 1u)) * pm * psec;
+  if ((s.hour >> h) & 1u) {
+    c += (uint32_t)popc64(s.minute & ((1ULL << mi) - 1ULL)) * psec;
+    if ((s.minute >> mi) & 1ULL) c += (uint32_t)popc64(s.second & ((2ULL << sc) - 1ULL));
+  }
+  return c;
+}
+// largest matching second-of-day <= sod, or -1
+CW_HD int32_t last_tod_le(const Spec& s, int32_t sod) {
+  const int32_t h = sod / 3600, mi = (sod % 3600) / 60, sc = sod % 60;
+  const int32_t top_s = 63 - clz64(s.second), top_m = 63 - clz64(s.minute);
+  if ((s.hour >> h) & 1u) {
+    if ((s.minute >> mi) & 1ULL) {
+      const uint64_t m = s.second & ((2ULL << sc) - 1ULL);
+      if (m) return h * 3600 + mi * 60 + (63 - clz64(m));
+    }
+    const uint64_t m = s.minute & ((1ULL << mi) - 1ULL);
+    if (m) return h * 3600 + (63 - clz64(m)) * 60 + top_s;
+  }
+  const uint32_t hm = s.hour & ((1u << h) - 1u);
+  if (hm) return (31 - clz32(hm)) * 3600 + top_m * 60 + top_s;
+  return -1;
+}
+
+// Fast-forward the chain of Next() calls from the fire time held in `w` towards `limit` (absolute, inclusive) as far
+// as that is provably identical to upstream's one-call-per-fire chain; advances *missed and leaves `w` on the last
+// fire counted (unchanged when nothing could be proven).  The caller continues with a literal Next() from there.
+//
+// Why it is exact.  From a fire time f, the chained Next(f) starts at f+1s in a matching month, day and hour.
+//  (1) While fires remain before the next local midnight and before the end of the zone period, the walk only runs
+//      the Add-based second/minute/hour loops: they visit absolute instants in order and test local fields, which
+//      advance uniformly inside one period, so the chain enumerates the remaining matching times of day in order.
+//      The one Date() call that can appear is the hour reset when f is hh:59:59 (f+1s is an exact hour start);
+//      specs that can fire at :59:59 therefore also need every instant of the stretch to be Walk::natural.
+//  (2) After the last fire of a day the walk wraps, always aligned, to the next local midnight (strictly inside the
+//      period) and crosses non-matching days with AddDate steps at hour 0 (no DST fix) and months with the Day()==1
+//      wrap; while all those midnights are natural in this period the chain visits exactly the matching days, and
+//      each such day's fires are enumerated by (1).  The 5-year limit can only bite between two matching days: the
+//      fast-forward stops before any day whose year exceeds (last fire year + 5) and lets the literal call decide.
+CW_HD void chain_fast_forward(const Spec& s, Walk& w, int64_t limit, uint32_t* missed) {
+  const bool edge59 = ((s.second >> 59) & 1ULL) && ((s.minute >> 59) & 1ULL);
+  // A fire produced while a loop stepped across a transition can sit on fields upstream never re-checked (e.g. the
+  // hour loop going 23h -> 01h over a midnight gap lands on a day that does not match).  The next call re-checks
+  // them from scratch, so nothing may be assumed about such a fire: only fast-forward from a fully matching one.
+  if (!(((s.month >> w.M) & 1u) && day_matches(s, w.D, w.dn) && ((s.hour >> w.hour()) & 1u) &&
+        ((s.minute >> w.minute()) & 1ULL) && ((s.second >> w.second()) & 1ULL)))
+    return;
+  // ---- (1) rest of the current local day, up to the period edge ----
+  const int64_t day_end = w.t + (86400 - w.sod);  // absolute instant of the next local midnight at this offset
+  {
+    int64_t lim_abs = limit < day_end - 1 ? limit : day_end - 1;
+    if (w.pe - 1 < lim_abs) lim_abs = w.pe - 1;
+    if (edge59 && !(w.natural(w.t + w.off) && w.natural(lim_abs + w.off))) return;
+    const int32_t lim_sod = w.sod + (int32_t)(lim_abs - w.t);
+    const int32_t last = last_tod_le(s, lim_sod);
+    if (last > w.sod) {
+      *missed = sat_add(*missed, count_tod_le(s, lim_sod) - count_tod_le(s, w.sod));
+      w.t += last - w.sod;
+      w.sod = last;
+    }
+  }
+  if (limit < day_end || day_end >= w.pe) return;
+
+  // ---- (2) whole following days whose midnights are natural in this period ----
+  const int64_t kFar = (int64_t)1 << 46;  // ~2.2 million years: outside every supported input
+  const int64_t xmax = w.pe == kOmega ? kFar : w.pe - 1 + (w.off < 0 ? w.off : 0);
+  const int64_t xmin = w.ps == kAlpha ? -kFar : w.ps + (w.off > 0 ? w.off : 0);
+  int64_t dhi64 = xmax / 86400; if (xmax % 86400 < 0) --dhi64;   // floor
+  int64_t dlo64 = xmin / 86400; if (xmin % 86400 > 0) ++dlo64;   // ceil
+  const int32_t dhi = (int32_t)dhi64, dlo = (int32_t)dlo64;      // days d with natural(d * 86400): dlo <= d <= dhi
+  int32_t cur = w.dn + 1;
+  if (cur < dlo || cur > dhi) return;
+
+  const bool lim_inside = limit < w.pe;
+  int32_t Ld = 0, Lsod = 0;
+  if (lim_inside) {
+    const int64_t L = limit + w.off;
+    int64_t q = L / 86400; if (L % 86400 < 0) --q;
+    Ld = (int32_t)q; Lsod = (int32_t)(L - q * 86400);
+  }
+  int32_t full_last = dhi - 1;  // last day whose closing midnight is still natural
+  if (lim_inside && Ld - 1 < full_last) full_last = Ld - 1;
+  const bool partial = lim_inside && Ld <= dhi && (!edge59 || w.natural(limit + w.off));
+
+  const uint32_t per_day = (uint32_t)popc32(s.hour) * (uint32_t)popc64(s.minute) * (uint32_t)popc64(s.second);
+  int32_t Y = w.Y, M = w.M, D = w.D + 1;
+  if (D > days_in_month(Y, M)) { D = 1; if (++M == 13) { M = 1; ++Y; } }
+  int32_t fire_year = w.Y;
+  uint64_t total = 0;
+  int32_t last_dn = INT32_MIN, last_sod = 0;
+  bool stopped = false;
+  while (cur <= full_last) {
+    const int32_t dim = days_in_month(Y, M);
+    const int32_t dend = (full_last - cur) < (dim - D) ? D + (full_last - cur) : dim;  // last day of month in range
+    if ((s.month >> M) & 1u) {
+      const uint32_t range = (uint32_t)(((2ULL << dend) - 1ULL) & ~((1ULL << D) - 1ULL));
+      const uint32_t dm = month_daymask(s, Y, M, cur - (D - 1)) & range;
+      if (dm) {
+        if (Y > fire_year + 5) { stopped = true; break; }
+        total += (uint64_t)popc32(dm) * per_day;
+        last_dn = cur - D + (31 - clz32(dm));
+        fire_year = Y;
+      }
+    }
+    cur += dend - D + 1;
+    D = dend + 1;
+    if (D > dim) { D = 1; if (++M == 13) { M = 1; ++Y; } }
+  }
+  if (last_dn != INT32_MIN) last_sod = last_tod_le(s, 86399);
+  if (!stopped && partial && cur == Ld) {  // the day holding `limit`: fires with time of day <= Lsod
+    if (((s.month >> M) & 1u) && day_matches(s, D, Ld) && Y <= fire_year + 5) {
+      const uint32_t c = count_tod_le(s, Lsod);
+      if (c) { total += c; last_dn = Ld; last_sod = last_tod_le(s, Lsod); }
+    }
+  }
+  if (last_dn == INT32_MIN) return;
+  *missed = sat_add(*missed, total);
+  w.dn = last_dn;
+  w.sod = last_sod;
+  w.t = (int64_t)last_dn * 86400 + last_sod - w.off;
+  civil_from_days(last_dn, w.Y, w.M, w.D);
+}
+
+// getNextSchedule + gates + decision for one Cron
+CW_HD UnmetOut unmet_decide(const Spec& s, const ZoneTable& zt, int32_t zone, const UnmetIn& in) {
+  UnmetOut o;
+  o.last = kZero; o.next = kZero; o.missed = 0; o.status = kStOk;
+  if (in.flags & kFlagDeleted) { o.decision = kDecGateDeleted; return o; }
+  if (in.flags & kFlagSuspend) { o.decision = kDecGateSuspended; return o; }
+  // now.After(deadline): now carries nanoseconds, the deadline is a whole second
+  if (in.deadline != kZero && (in.now > in.deadline || (in.now == in.deadline && in.now_nsec > 0))) {
+    o.decision = kDecGateDeadline;
+    return o;
+  }
+  Walk w;
+  if (zone == 0) w.bind_utc(); else w.bind_zone(zt, zone);
+
+  if (in.earliest > in.now) {  // :404-406
+    o.next = next_from(s, w, in.now, false);
+    o.status = kStEarliestAfterNow;
+    o.decision = kDecRequeueOnly;
+    return o;
+  }
+  // :409  for t := sched.Next(earliest); !t.After(now); t = sched.Next(t)
+  int64_t t = next_from(s, w, in.earliest, false);
+  while (t == kZero || t <= in.now) {
+    if (t == kZero) {  // :410-412
+      o.last = kZero; o.missed = 0; o.status = kStUnschedulable; o.decision = kDecErrUnschedulable;
+      return o;
+    }
+    o.missed = sat_add(o.missed, 1);
+    chain_fast_forward(s, w, in.now, &o.missed);
+    o.last = w.t;
+    t = next_from(s, w, w.t, true);
+  }
+  o.next = next_from(s, w, in.now, false);  // :436
+  if (o.last == kZero) o.decision = kDecRequeueOnly;                                        // :196-199
+  else if (in.policy == kPolicyForbid && in.active > 0) o.decision = kDecSkipForbid;        // :204-207
+  else if (in.policy == kPolicyReplace) o.decision = kDecReplaceCreate;                     // :210-220
+  else o.decision = kDecCreate;
+  return o;
+}
+
+}  // namespace cronwalk

@@ -1,0 +1,30 @@
+// zone_table.h -- host-side builder of the flattened IANA zone table the kernels read (pure C++17, no CUDA).
+//
+// Replaces, for the batched path, what the reference gets from Go's time.LoadLocation when a schedule carries a
+// TZ=/CRON_TZ= prefix (robfig/cron v3.0.1 parser.go, reached from internal/controller/cron_controller.go:392) and
+// from time.Local otherwise.  Each zone becomes a sorted list of (when, utc offset) periods: the TZif 64-bit body,
+// Go's "first zone" rule before the first transition, and the footer POSIX-TZ rule expanded year by year up to a
+// horizon, so that the device never parses a rule string.
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace b200cron {
+
+struct HostZoneTable {
+  std::vector<std::string> names;  // names[0] == "UTC"; the rest sorted
+  std::vector<int32_t> zstart;     // names.size() + 1 entries
+  std::vector<int64_t> when;       // first entry of every zone is INT64_MIN
+  std::vector<int32_t> off;
+  int64_t horizon = 0;             // unix second up to which footer rules were expanded
+  int horizon_year = 0;
+
+  int find(const std::string& name) const;  // -1 when unknown
+};
+
+// Scans `zoneinfo_dir` recursively for TZif files (skipping posix/ and right/), builds the table.
+// Returns false and fills `err` when the directory is unusable.
+bool build_zone_table(const std::string& zoneinfo_dir, int horizon_year, HostZoneTable* out, std::string* err);
+
+}  // namespace b200cron

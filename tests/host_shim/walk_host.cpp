@@ -1,0 +1,90 @@
+// walk_host.cpp -- TEST-ONLY host build of the kernels' per-spec walk (cron_walk.cuh) and zone table builder.
+//
+// This box has no GPU, so the CPU test suite compiles the *same* __host__ __device__ source the kernels use with g++
+// and checks it against the oracle.  It is test infrastructure: nothing in the product library links or calls it,
+// and the product has no CPU execution path.
+#include <cstdint>
+#include <cstring>
+#include <string>
+
+#include "cron_walk.cuh"
+#include "unmet_walk.cuh"
+#include "zone_table.h"
+
+using namespace cronwalk;
+
+extern "C" {
+
+void* shim_table_build(const char* dir, int horizon_year) {
+  auto* t = new b200cron::HostZoneTable();
+  std::string err;
+  if (!b200cron::build_zone_table(dir, horizon_year, t, &err)) {
+    delete t;
+    return nullptr;
+  }
+  return t;
+}
+void shim_table_free(void* t) { delete (b200cron::HostZoneTable*)t; }
+int shim_zone_count(void* t) { return (int)((b200cron::HostZoneTable*)t)->names.size(); }
+const char* shim_zone_name(void* t, int i) { return ((b200cron::HostZoneTable*)t)->names[i].c_str(); }
+int shim_zone_find(void* t, const char* name) { return ((b200cron::HostZoneTable*)t)->find(name); }
+int shim_zone_entries(void* t, int z, const int64_t** when, const int32_t** off) {
+  auto* h = (b200cron::HostZoneTable*)t;
+  *when = h->when.data() + h->zstart[z];
+  *off = h->off.data() + h->zstart[z];
+  return h->zstart[z + 1] - h->zstart[z];
+}
+int64_t shim_total_entries(void* t) { return (int64_t)((b200cron::HostZoneTable*)t)->when.size(); }
+
+static ZoneTable view(void* t) {
+  auto* h = (b200cron::HostZoneTable*)t;
+  ZoneTable z;
+  z.when = h->when.data();
+  z.off = h->off.data();
+  z.zstart = h->zstart.data();
+  z.nzones = (int32_t)h->names.size();
+  z.horizon = h->horizon;
+  return z;
+}
+
+void shim_next_n(void* table, const uint64_t* const masks[6], const int32_t* zone_id, const int64_t* from, size_t n,
+                 int k, int64_t* out) {
+  ZoneTable zt = view(table);
+  for (size_t i = 0; i < n; ++i) {
+    Spec s = make_spec(masks[0][i], masks[1][i], masks[2][i], masks[3][i], masks[4][i], masks[5][i]);
+    Walk w;
+    const int32_t z = zone_id ? zone_id[i] : 0;
+    if (z == 0) w.bind_utc(); else w.bind_zone(zt, z);
+    int64_t t = from[i];
+    bool resident = false;
+    for (int q = 0; q < k; ++q) {
+      if (t != kZero) {
+        t = next_from(s, w, t, resident);
+        resident = true;
+      }
+      out[i * (size_t)k + q] = t;
+    }
+  }
+}
+
+void shim_unmet(void* table, const uint64_t* const masks[6], const int32_t* zone_id, const int64_t* earliest,
+                int64_t now, int32_t now_nsec, const uint8_t* policy, const uint32_t* active, const uint8_t* flags,
+                const int64_t* deadline, size_t n, int64_t* last, int64_t* next, uint32_t* missed, uint8_t* status,
+                uint8_t* decision) {
+  ZoneTable zt = view(table);
+  for (size_t i = 0; i < n; ++i) {
+    Spec s = make_spec(masks[0][i], masks[1][i], masks[2][i], masks[3][i], masks[4][i], masks[5][i]);
+    UnmetIn in;
+    in.earliest = earliest[i];
+    in.now = now;
+    in.now_nsec = now_nsec;
+    in.policy = policy ? policy[i] : 0;
+    in.active = active ? active[i] : 0;
+    in.flags = flags ? flags[i] : 0;
+    in.deadline = deadline ? deadline[i] : kZero;
+    UnmetOut o = unmet_decide(s, zt, zone_id ? zone_id[i] : 0, in);
+    last[i] = o.last; next[i] = o.next; missed[i] = o.missed; status[i] = o.status; decision[i] = o.decision;
+  }
+}
+
+}  // extern "C"

@@ -1,0 +1,146 @@
+"""CPU checks of the kernels' unmet-enumeration source (host build) against the oracle's literal getNextSchedule
+chain (cron_controller.go:389-437) + gates/decision (:163-220)."""
+import numpy as np
+import pytest
+
+from cron_operator_b200 import synth
+from oracle import pyoracle as po
+from tests import shim
+from tests.test_walk_host import EDGE_ZONES, NAMES, _masks_of
+
+ts = synth.ts
+KEYS = ("last", "next", "missed", "status", "decision")
+
+
+def _cmp(got, want, ctx=""):
+    for k in KEYS:
+        bad = np.nonzero(got[k] != want[k])[0]
+        assert len(bad) == 0, (ctx, k, bad[:5], got[k][bad[:5]], want[k][bad[:5]])
+
+
+def test_K3_through_kernel_source():
+    now = ts(2026, 1, 1, 12)
+    m = _masks_of(["*/1 * * * *", "0 0 30 2 *", "*/5 * * * *"])
+    got = shim.unmet(m, np.full(3, now - 300), now)
+    assert got["last"].tolist() == [now, po.ZERO, now]
+    assert got["next"].tolist() == [now + 60, po.ZERO, now + 300]
+    assert got["missed"].tolist() == [5, 0, 1]
+    assert got["status"].tolist() == [0, 1, 0]
+    assert got["decision"].tolist() == [po.DEC_CREATE, po.DEC_ERR_UNSCHEDULABLE, po.DEC_CREATE]
+
+
+def test_gates_and_policies():
+    now = ts(2026, 1, 1, 12)
+    m = _masks_of(["*/5 * * * *"] * 10)
+    earliest = np.array([now - 300] * 8 + [now + 10, now - 1], dtype=np.int64)
+    policy = np.array([0, 1, 1, 2, 2, 0, 0, 0, 0, 0], dtype=np.uint8)
+    active = np.array([3, 0, 2, 0, 4, 0, 0, 0, 0, 0], dtype=np.uint32)
+    flags = np.array([0, 0, 0, 0, 0, 1, 2, 0, 0, 0], dtype=np.uint8)
+    deadline = np.array([po.ZERO] * 7 + [now - 1, po.ZERO, now], dtype=np.int64)
+    for nsec in (0, 5):
+        got = shim.unmet(m, earliest, now, nsec, policy, active, flags, deadline)
+        want = po.batch_unmet(m, earliest, now, nsec, policy, active, flags, deadline)
+        _cmp(got, want)
+    got = shim.unmet(m, earliest, now, 0, policy, active, flags, deadline)
+    assert got["decision"].tolist() == [po.DEC_CREATE, po.DEC_CREATE, po.DEC_SKIP_FORBID, po.DEC_REPLACE_CREATE,
+                                        po.DEC_REPLACE_CREATE, po.DEC_GATE_SUSPENDED, po.DEC_GATE_DELETED,
+                                        po.DEC_GATE_DEADLINE, po.DEC_REQUEUE_ONLY, po.DEC_CREATE]
+    # deadline == now: only a sub-second "now" is after it
+    got = shim.unmet(m, earliest, now, 1, policy, active, flags, deadline)
+    assert got["decision"][9] == po.DEC_GATE_DEADLINE
+
+
+def test_unmet_utc_random_short_backlog():
+    n = 6000
+    masks = synth.gen_specs(n, seed=31, dense_minutes=0.3)
+    now = ts(2026, 3, 29, 12)
+    earliest = now - synth.gen_times(n, 0, 3 * 86400, seed=31)
+    got = shim.unmet(masks, earliest, now)
+    want = po.batch_unmet(masks, earliest, now)
+    _cmp(got, want)
+    assert want["missed"].max() > 100 and (want["status"] == 1).sum() > 0
+
+
+def test_unmet_utc_long_backlog_sparse():
+    """multi-year backlogs on specs that fire at most a few times a day (keeps the literal oracle affordable)"""
+    n = 1500
+    masks = synth.gen_specs(n, seed=32)
+    masks[1] = np.uint64(1) << (synth.gen_times(n, 0, 60, seed=32, stream=400).astype(np.uint64))  # one minute value
+    masks[2] &= np.uint64(0x800000000000000F) | (np.uint64(1) << np.uint64(13))                      # few hours
+    masks[2] = np.where(masks[2] & np.uint64(0xFFFFFF), masks[2], np.uint64(1 << 7))
+    now = ts(2031, 7, 4, 9, 30)
+    earliest = now - synth.gen_times(n, 0, 9 * 366 * 86400, seed=33)
+    got = shim.unmet(masks, earliest, now)
+    want = po.batch_unmet(masks, earliest, now)
+    _cmp(got, want)
+
+
+def test_unmet_year_limit_inside_backlog():
+    # "0 0 29 2 *" from 2095: fires 2096-02-29, then the next one (2104) is beyond the 5-year limit -> the chain
+    # hits the zero time and the whole call is "unschedulable" even though one run was missed
+    m = _masks_of(["0 0 29 2 *", "0 0 29 2 *", "0 0 29 2 *"])
+    earliest = np.array([ts(2095), ts(2095), ts(2019)], dtype=np.int64)
+    now_cases = [ts(2097), ts(2104, 3, 1)]
+    for now in now_cases:
+        got = shim.unmet(m, earliest, now)
+        want = po.batch_unmet(m, earliest, now)
+        _cmp(got, want, now)
+    assert shim.unmet(m, earliest, ts(2104, 3, 1))["status"].tolist() == [1, 1, 1]
+
+
+@pytest.mark.parametrize("name", EDGE_ZONES)
+def test_unmet_windows_across_transitions(name):
+    z = NAMES.index(name)
+    when, _ = shim.zone_entries(z)
+    trans = [int(w) for w in when if ts(2021) < w < ts(2041)][:24]
+    texts = ["*/20 * * * *", "0 * * * *", "30 2 * * *", "0 0 * * *", "0 1 * * *", "59 23 * * *", "0 0 1 * *",
+             "15 3 * * 0", "0 */2 * * *", "30 0 * * *", "45 1-3 25-31 * 0", "0 3 * * *", "0 0 2 * *", "*/30 0-4 * * *"]
+    base = _masks_of(texts)
+    # (earliest offset, now offset) relative to the transition
+    wins = [(-3 * 86400, 3 * 86400), (-40 * 86400, 1), (-5, 86400 * 2), (-86400, -1), (-7200, 7200), (0, 86400),
+            (-20 * 86400, 20 * 86400), (-3600, 0), (1, 5 * 86400)]
+    cases = [(t + a, t + b) for t in trans for a, b in wins]
+    for now_off in range(len(wins)):
+        sel = [c for i, c in enumerate(cases) if i % len(wins) == now_off]
+        for (e, now) in sel[:6]:
+            S = len(texts)
+            got = shim.unmet(base, np.full(S, e), now, zone_id=np.full(S, z, np.int32))
+            want = po.batch_unmet(base, np.full(S, e), now, zone_id=np.full(S, z, np.int32), zone_names=NAMES)
+            _cmp(got, want, (name, e, now))
+
+
+def test_unmet_seconds_field_across_transitions():
+    texts = ["*/20 * * * * *", "59 59 * * * *", "59 59 23 * * *", "0 30 0 * * *", "59 59 1 * * 0", "30 */15 1-3 * * *"]
+    base = _masks_of(texts, with_seconds=True)
+    for name in ["America/New_York", "Australia/Lord_Howe", "Africa/Cairo", "America/Havana", "Atlantic/Azores"]:
+        z = NAMES.index(name)
+        when, _ = shim.zone_entries(z)
+        for t in [int(w) for w in when if ts(2024) < w < ts(2028)]:
+            for a, b in [(-7200, 7200), (-86400, 3600), (-3, 3), (-90000, 90000)]:
+                S = len(texts)
+                got = shim.unmet(base, np.full(S, t + a), t + b, zone_id=np.full(S, z, np.int32))
+                want = po.batch_unmet(base, np.full(S, t + a), t + b, zone_id=np.full(S, z, np.int32), zone_names=NAMES)
+                _cmp(got, want, (name, t, a, b))
+
+
+def test_unmet_C4_shape_mixed_zones():
+    """C4-shaped sample: 30-day backlog, now inside a European DST day, mixed zones, policies, gates"""
+    n = 3000
+    masks = synth.gen_specs(n, seed=41, dense_minutes=0.5)
+    # keep the literal oracle affordable: dense-minute specs fire in a few hours only
+    dense = (masks[1] & np.uint64((1 << 60) - 1)).astype(np.uint64)
+    many = np.array([bin(int(x)).count("1") for x in dense]) > 6
+    masks[2] = np.where(many, masks[2] & np.uint64(0x800000000000000E), masks[2])
+    masks[2] = np.where(masks[2] & np.uint64(0xFFFFFF), masks[2], np.uint64(1 << 2))
+    dst = [z for z in range(1, len(NAMES)) if (shim.zone_entries(z)[0] > ts(2030)).any()]
+    zid = synth.gen_zone_ids(n, len(NAMES), np.array(dst), seed=41)
+    now = ts(2026, 3, 29, 12)
+    earliest = now - 30 * 86400 + synth.gen_times(n, -86400, 86400, seed=41)
+    rng = np.random.default_rng(41)
+    policy = rng.integers(0, 3, n).astype(np.uint8)
+    active = rng.choice([0, 1, 2, 3, 4], size=n, p=[0.6, 0.3, 0.04, 0.03, 0.03]).astype(np.uint32)
+    flags = (rng.random(n) < 0.02).astype(np.uint8)
+    deadline = np.where(rng.random(n) < 0.01, now - 100, po.ZERO).astype(np.int64)
+    got = shim.unmet(masks, earliest, now, 0, policy, active, flags, deadline, zone_id=zid)
+    want = po.batch_unmet(masks, earliest, now, 0, policy, active, flags, deadline, zone_id=zid, zone_names=NAMES)
+    _cmp(got, want)
