@@ -1,0 +1,318 @@
+#!/usr/bin/env python
+"""bench.py -- schedule evaluations/sec of the batched cron-schedule path on B200 (BASELINE.json metric).
+
+A "step" is one pass of the hot path over one batch of synthetic specs.  Workload at every N: BASELINE config C2
+(1M random 5-field UTC cron specs, next single fire time) per GPU (weak scaling: each rank owns its own contiguous
+1M-spec shard of one big synthetic spec list; no collective on the data path).
+
+  value     evals/s with inputs resident in HBM, timed with CUDA events around the kernel on its launch stream,
+            L2 flushed (256 MiB memset) between steps, max over ranks
+  e2e       the same metric through the reference-facing C ABI with pinned HOST buffers (H2D + kernel + D2H inside)
+  roofline  algorithmic bytes (64 B/eval) / kernel time vs MEASURED_PEAKS.json hbm_gbs
+  cpu_baseline  the C restatement of the reference's Go path (oracle/) on this box's host cores (rank 0, N=1)
+
+--impl reference times that CPU path alone (the reference is Go; no Go toolchain exists on this image, so the
+reference arm is the oracle port, kind "port").
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from cron_operator_b200 import synth  # noqa: E402
+
+N_SPECS = 1_000_000          # C2
+BYTES_PER_EVAL = 64          # 48 masks + 8 from + 8 out
+T_LO, T_HI = synth.ts(2024), synth.ts(2034)
+METRIC = "schedule_evals_per_sec"
+UNIT = "evals/s"
+WORKLOAD = "C2: 1M random 5-field UTC cron specs, next single fire time (per GPU)"
+
+
+def peaks():
+    try:
+        p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs"""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx, self.rows, self.p = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                       "-lms", "200", "-i", str(self.idx)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.p = None
+
+    def _pump(self):
+        for line in self.p.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.p:
+            time.sleep(0.25)
+            self.p.terminate()
+        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) < 9:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_reference(steps: int, warmup: int, threads: int | None = None):
+    """times the oracle (C restatement of the Go path) on the C2 workload with all host threads"""
+    from oracle import pyoracle as po
+    threads = threads or po.cpu_count()
+    masks = synth.gen_specs(N_SPECS)
+    frm = synth.gen_times(N_SPECS, T_LO, T_HI)
+    for _ in range(warmup):
+        po.batch_next_n(masks, frm, 1, threads=threads)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        po.batch_next_n(masks, frm, 1, threads=threads)
+    dt = time.perf_counter() - t0
+    return N_SPECS * steps / dt, dt / steps * 1e3, threads
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    v, ms, threads = cpu_reference(args.steps, args.warmup)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "int64", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "note": "CPU path; every step is the full 1M-spec C2 batch on host cores"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": f"full C2 batch ({N_SPECS} specs) x {args.steps} steps; C restatement of "
+                                   "robfig/cron v3.0.1 + Go time (no Go toolchain on this image)"},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def extra_kernels(ctx, torch, st, peak):
+    """kernel-only numbers for the other BASELINE configs (bounded sizes), each with its roofline fraction"""
+    out = {}
+    names = ctx.zone_names
+    dst = np.array([z for z in range(1, len(names)) if (ctx.zone_periods(z)[0] > synth.ts(2030)).any()])
+
+    def timed(fn, reps=5):
+        fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        best = 1e30
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+        for _ in range(reps):
+            flush.zero_()
+            e0.record()
+            fn()
+            e1.record()
+            torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        return best * 1e-3
+
+    # C3 shape: seconds field, mixed zones, K = 16 (16M specs instead of 100M: 3 GB resident)
+    n, k = 16_000_000, 16
+    masks = synth.gen_specs(n, seed=3, with_seconds=True)
+    zid = synth.gen_zone_ids(n, len(names), dst, seed=3)
+    frm = synth.gen_times(n, synth.ts(2024), synth.ts(2036), seed=3)
+    dm, dz, df = torch.from_numpy(masks.view(np.int64)).cuda(), torch.from_numpy(zid).cuda(), torch.from_numpy(frm).cuda()
+    o = torch.empty((n, k), dtype=torch.int64, device="cuda")
+    s = timed(lambda: ctx.next_n_dev(dm, df, o, k, dz, stream=st))
+    out["C3_nextN_k16_zoned"] = {"specs": n, "evals_per_s": n * k / s, "specs_per_s": n / s, "ms": s * 1e3,
+                                 "bytes_per_spec": 188, "roofline_frac": 188 * n / s / 1e9 / peak}
+    # C4 shape: unmet + decision, 30-day backlog, now inside a European DST day
+    n4 = 10_000_000
+    m4 = synth.gen_specs(n4, seed=41, dense_minutes=0.5)
+    z4 = synth.gen_zone_ids(n4, len(names), dst, seed=41)
+    now = synth.ts(2026, 3, 29, 12)
+    e4 = now - 30 * 86400 + synth.gen_times(n4, -86400, 86400, seed=41)
+    rng = np.random.default_rng(41)
+    t = lambda a: torch.from_numpy(a).cuda()  # noqa: E731
+    dm4, dz4, de4 = t(m4.view(np.int64)), t(z4), t(e4)
+    dp, da = t(rng.integers(0, 3, n4).astype(np.uint8)), t(rng.choice([0, 1, 2], size=n4, p=[.6, .3, .1]).astype(np.uint32))
+    dfl, ddl = t((rng.random(n4) < 0.02).astype(np.uint8)), t(np.where(rng.random(n4) < 0.01, now - 100, -2**63).astype(np.int64))
+    o4 = dict(last=torch.empty(n4, dtype=torch.int64, device="cuda"), next=torch.empty(n4, dtype=torch.int64, device="cuda"),
+              missed=torch.empty(n4, dtype=torch.int32, device="cuda"), status=torch.empty(n4, dtype=torch.uint8, device="cuda"),
+              decision=torch.empty(n4, dtype=torch.uint8, device="cuda"))
+    s = timed(lambda: ctx.unmet_since_dev(dm4, de4, now, o4, 0, dp, da, dfl, ddl, dz4, stream=st))
+    missed_total = int(o4["missed"].to(torch.int64).sum().item())
+    out["C4_unmet_since"] = {"specs": n4, "specs_per_s": n4 / s, "ms": s * 1e3, "bytes_per_spec": 96,
+                             "roofline_frac": 96 * n4 / s / 1e9 / peak, "missed_runs_counted": missed_total,
+                             "equivalent_literal_next_calls_per_s": (missed_total + 2 * n4) / s,
+                             "note": "missed runs are counted analytically; not literal Next() calls"}
+    del dm, dz, df, o, dm4, dz4, de4, o4
+    # C5 shape: history sort/prune, U{0..16} records per Cron, historyLimit 10 (8M segments)
+    ns = 8_000_000
+    lens = rng.integers(0, 17, ns)
+    seg = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    m = int(seg[-1])
+    key = (1_760_000_000 - rng.integers(0, 86400, m)).astype(np.int64)
+    ds, dk, dl = t(seg.view(np.int64)), t(key), t(np.full(ns, 10, np.int64))
+    perm, keep = torch.empty(m, dtype=torch.int32, device="cuda"), torch.empty(m, dtype=torch.uint8, device="cuda")
+    s = timed(lambda: ctx.history_prune_dev(ds, dk, dl, perm, keep, stream=st))
+    out["C5_history_prune"] = {"segments": ns, "records": m, "records_per_s": m / s, "ms": s * 1e3,
+                               "roofline_frac": (13 * m + 16 * ns) / s / 1e9 / peak}
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-extra", action="store_true", help="skip the C3/C4/C5 kernel-only measurements")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    from cron_operator_b200 import api
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    ctx = api.Context(devices=[local])
+    st = torch.cuda.current_stream().cuda_stream
+    peak, peak_src = peaks()
+
+    # this rank's contiguous shard of the synthetic spec list
+    masks = synth.gen_specs(N_SPECS, start=rank * N_SPECS)
+    frm = synth.gen_times(N_SPECS, T_LO, T_HI, start=rank * N_SPECS)
+    d_masks = torch.from_numpy(masks.view(np.int64)).cuda()
+    d_from = torch.from_numpy(frm).cuda()
+    d_out = torch.empty((N_SPECS, 1), dtype=torch.int64, device="cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step():
+        ctx.next_n_dev(d_masks, d_from, d_out, 1, None, stream=st)
+
+    for _ in range(args.warmup):
+        flush.zero_()
+        step()
+    ctx.sync_check(stream=st)
+
+    # ---- kernel-resident timing ----
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    launches0 = ctx.launch_count
+    barrier()
+    for a, b in ev:
+        flush.zero_()
+        a.record()
+        step()
+        b.record()
+    barrier()
+    launches = ctx.launch_count - launches0
+    ctx.sync_check(stream=st)
+    dev_s = sum(a.elapsed_time(b) for a, b in ev) * 1e-3
+    kernel_ms = [a.elapsed_time(b) for a, b in ev]
+
+    # ---- end to end through the host-pointer C ABI (pinned host buffers) ----
+    h_masks, h_from, h_out = api.PinnedArray((6, N_SPECS), np.uint64), api.PinnedArray(N_SPECS, np.int64), api.PinnedArray((N_SPECS, 1), np.int64)
+    h_masks.array[:] = masks
+    h_from.array[:] = frm
+    for _ in range(args.warmup):
+        ctx.next_n(h_masks.array, h_from.array, 1, out=h_out.array)
+    e2e_steps = args.steps
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        ctx.next_n(h_masks.array, h_from.array, 1, out=h_out.array)
+    e2e_s = time.perf_counter() - t0
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    assert np.array_equal(h_out.array, d_out.cpu().numpy()), "host-pointer and device-pointer paths disagree"
+
+    if world > 1:
+        tt = torch.tensor([dev_s, e2e_s], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dev_s, e2e_s = tt.tolist()
+
+    if rank == 0:
+        value = world * N_SPECS * args.steps / dev_s
+        e2e = world * N_SPECS * e2e_steps / e2e_s
+        avg_kernel_s = dev_s / args.steps
+        achieved = BYTES_PER_EVAL * N_SPECS / avg_kernel_s / 1e9
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": avg_kernel_s * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "int64", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "specs_per_gpu": N_SPECS, "k": 1, "zone": "UTC",
+                       "l2": "flushed between steps with a 256 MiB memset (not timed)",
+                       "timing": "CUDA events around the kernel on its launch stream, summed over steps, max over ranks",
+                       "parallelism": f"specs sharded contiguously over {world} GPU(s), no collective"},
+            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": 56 * N_SPECS, "d2h_bytes_per_step": 8 * N_SPECS,
+                    "ms_per_step": e2e_s / e2e_steps * 1e3, "how": "b200cron_next_n on pinned host buffers, wall clock"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_source": peak_src, "kernel": "next_n_kernel<1,true>",
+                         "algorithmic_bytes_per_launch": BYTES_PER_EVAL * N_SPECS,
+                         "kernel_ms_min_med_max": [min(kernel_ms), float(np.median(kernel_ms)), max(kernel_ms)]},
+            "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu:
+            reps = 20
+            v, ms, threads = cpu_reference(reps, 1)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                                    "sample": f"full C2 batch ({N_SPECS} specs) x {reps} reps, all host threads; C "
+                                              "restatement of robfig/cron v3.0.1 + Go time (no Go toolchain here)"}
+        if world == 1 and not args.no_extra:
+            try:
+                line["extra"] = extra_kernels(ctx, torch, st, peak)
+            except Exception as e:  # the headline must survive a failure of the side measurements
+                line["extra"] = {"error": repr(e)}
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

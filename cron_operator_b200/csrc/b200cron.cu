@@ -1,0 +1,550 @@
+// b200cron.cu -- context, host<->device plumbing and the extern "C" entry points of libb200cron.so (include/b200cron.h).
+//
+// Host-pointer calls shard `n` contiguously over the context's devices (no collective: every spec is independent,
+// SURVEY.md section 8e) and, per device, pipeline chunks over kSlots streams so that H2D copies, the kernel and D2H
+// copies of neighbouring chunks overlap.  `_dev` calls only enqueue a kernel on the caller's stream.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/b200cron.h"
+#include "kernels.cuh"
+#include "zone_table.h"
+
+namespace {
+
+using namespace b200cron;
+
+constexpr int kSlots = 3;
+constexpr size_t kChunk = 1u << 18;  // specs per pipelined chunk of the host-pointer calls
+
+std::string g_create_error;
+
+struct Slot {
+  cudaStream_t stream = nullptr;
+  void* buf = nullptr;  // device staging
+  size_t cap = 0;
+};
+
+struct Device {
+  int id = 0;
+  cudaStream_t stream = nullptr;  // default stream of the _dev entry points
+  int64_t* d_when = nullptr;
+  int32_t* d_off = nullptr;
+  int32_t* d_zstart = nullptr;
+  int* d_err = nullptr;
+  int* h_err = nullptr;  // pinned mirror
+  Slot slots[kSlots];
+  ZoneTable zt{};
+};
+
+}  // namespace
+
+struct b200cron_ctx {
+  std::vector<Device> devs;
+  HostZoneTable zones;
+  std::string error;
+  std::mutex mu;
+  std::atomic<uint64_t> launches{0};
+};
+
+namespace {
+
+int fail(b200cron_ctx* ctx, int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  if (ctx) ctx->error = buf; else g_create_error = buf;
+  return code;
+}
+
+#define CU(ctx, call)                                                                                  \
+  do {                                                                                                 \
+    cudaError_t e_ = (call);                                                                           \
+    if (e_ != cudaSuccess)                                                                             \
+      return fail(ctx, B200CRON_ECUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+  } while (0)
+
+size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+int ensure_slot(b200cron_ctx* ctx, Slot& s, size_t bytes) {
+  if (bytes <= s.cap) return 0;
+  if (s.buf) CU(ctx, cudaFree(s.buf));
+  s.buf = nullptr;
+  s.cap = 0;
+  CU(ctx, cudaMalloc(&s.buf, bytes));
+  s.cap = bytes;
+  return 0;
+}
+
+bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// ---- launches -------------------------------------------------------------------------------------------------
+template <int KT>
+cudaError_t launch_next_kt(bool vec, unsigned grid, size_t smem, cudaStream_t st, const MaskPlanes& m,
+                           const int32_t* zone, const int64_t* from, size_t n, int k, int64_t* out,
+                           const ZoneTable& zt, int* err) {
+  if (vec) {
+    if (smem > 48 * 1024)
+      cudaFuncSetAttribute(next_n_kernel<KT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    next_n_kernel<KT, true><<<grid, kNextThreads, smem, st>>>(m, zone, from, n, k, out, zt, err);
+  } else {
+    if (smem > 48 * 1024)
+      cudaFuncSetAttribute(next_n_kernel<KT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    next_n_kernel<KT, false><<<grid, kNextThreads, smem, st>>>(m, zone, from, n, k, out, zt, err);
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t launch_next(b200cron_ctx* ctx, const Device& d, cudaStream_t st, const MaskPlanes& m, const int32_t* zone,
+                        const int64_t* from, size_t n, int k, int64_t* out) {
+  if (n == 0) return cudaSuccess;
+  bool vec = aligned16(from) && aligned16(out) && (!zone || (reinterpret_cast<uintptr_t>(zone) & 7u) == 0);
+  for (int p = 0; p < 6; ++p) vec = vec && aligned16(m.p[p]);
+  const unsigned grid = (unsigned)((n + kNextTile - 1) / kNextTile);
+  const size_t smem = k == 1 ? 0 : (size_t)kNextTile * k * sizeof(int64_t);
+  ctx->launches.fetch_add(1, std::memory_order_relaxed);
+  switch (k) {
+    case 1: return launch_next_kt<1>(vec, grid, smem, st, m, zone, from, n, k, out, d.zt, d.d_err);
+    case 2: return launch_next_kt<2>(vec, grid, smem, st, m, zone, from, n, k, out, d.zt, d.d_err);
+    case 4: return launch_next_kt<4>(vec, grid, smem, st, m, zone, from, n, k, out, d.zt, d.d_err);
+    case 8: return launch_next_kt<8>(vec, grid, smem, st, m, zone, from, n, k, out, d.zt, d.d_err);
+    case 16: return launch_next_kt<16>(vec, grid, smem, st, m, zone, from, n, k, out, d.zt, d.d_err);
+    case 32: return launch_next_kt<32>(vec, grid, smem, st, m, zone, from, n, k, out, d.zt, d.d_err);
+    default: return launch_next_kt<0>(vec, grid, smem, st, m, zone, from, n, k, out, d.zt, d.d_err);
+  }
+}
+
+cudaError_t launch_unmet(b200cron_ctx* ctx, const Device& d, cudaStream_t st, const UnmetArgs& a) {
+  if (a.n == 0) return cudaSuccess;
+  const unsigned grid = (unsigned)((a.n + kUnmetThreads - 1) / kUnmetThreads);
+  ctx->launches.fetch_add(1, std::memory_order_relaxed);
+  unmet_kernel<<<grid, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_history(b200cron_ctx* ctx, cudaStream_t st, const uint64_t* seg_off, const int64_t* key,
+                           const int64_t* limit, size_t nseg, uint32_t* perm, uint8_t* keep) {
+  if (nseg == 0) return cudaSuccess;
+  const unsigned grid = (unsigned)((nseg + kHistSegs - 1) / kHistSegs);
+  ctx->launches.fetch_add(1, std::memory_order_relaxed);
+  history_prune_kernel<<<grid, kHistThreads, 0, st>>>(seg_off, key, limit, nseg, perm, keep);
+  return cudaGetLastError();
+}
+
+int check_err_flags(b200cron_ctx* ctx) {
+  int bits = 0;
+  for (Device& d : ctx->devs) {
+    bits |= *d.h_err;
+    *d.h_err = 0;
+  }
+  if (bits & kErrZone) return fail(ctx, B200CRON_ERANGE, "zone_id outside [0, %d)", (int)ctx->zones.names.size());
+  if (bits & kErrRange)
+    return fail(ctx, B200CRON_ERANGE,
+                "time outside the supported range (years 1..9999; zoned evaluations must stay below year %d)",
+                ctx->zones.horizon_year - 6);
+  return B200CRON_OK;
+}
+
+// fetch the device error word into the pinned mirror and clear it on the device (enqueued on `st`)
+cudaError_t collect_err(Device& d, cudaStream_t st) {
+  cudaError_t e = cudaMemcpyAsync(d.h_err, d.d_err, sizeof(int), cudaMemcpyDeviceToHost, st);
+  if (e != cudaSuccess) return e;
+  return cudaMemsetAsync(d.d_err, 0, sizeof(int), st);
+}
+
+struct Shard {
+  size_t lo, hi;
+};
+Shard shard_of(size_t n, int g, int G) {
+  // contiguous, even-sized boundaries so that 128-bit loads stay aligned on every device
+  size_t lo = n * (size_t)g / (size_t)G, hi = n * (size_t)(g + 1) / (size_t)G;
+  lo &= ~(size_t)1;
+  if (g + 1 < G) hi &= ~(size_t)1;
+  return {lo, hi};
+}
+
+Device* device_at(b200cron_ctx* ctx, int dev_index) {
+  if (!ctx || dev_index < 0 || dev_index >= (int)ctx->devs.size()) return nullptr;
+  return &ctx->devs[dev_index];
+}
+
+}  // namespace
+
+// =================================================================================================================
+// context
+// =================================================================================================================
+extern "C" int b200cron_ctx_create(const int* devices, int ndev, const char* zoneinfo_dir, int horizon_year,
+                                   b200cron_ctx** out) {
+  if (!out) return B200CRON_EINVAL;
+  *out = nullptr;
+  int count = 0;
+  cudaError_t ce = cudaGetDeviceCount(&count);
+  if (ce != cudaSuccess || count == 0)
+    return fail(nullptr, B200CRON_ECUDA, "no usable CUDA device (%s); this library has no CPU path",
+                ce == cudaSuccess ? "device count is 0" : cudaGetErrorString(ce));
+  std::vector<int> ids;
+  if (!devices || ndev <= 0) {
+    int cur = 0;
+    CU(nullptr, cudaGetDevice(&cur));
+    ids.push_back(cur);
+  } else {
+    for (int i = 0; i < ndev; ++i) {
+      if (devices[i] < 0 || devices[i] >= count) return fail(nullptr, B200CRON_EINVAL, "device %d does not exist", devices[i]);
+      ids.push_back(devices[i]);
+    }
+  }
+  std::string dir = zoneinfo_dir ? zoneinfo_dir : (getenv("ZONEINFO") ? getenv("ZONEINFO") : "/usr/share/zoneinfo");
+  if (horizon_year <= 0) horizon_year = 2200;
+  if (horizon_year < 2040 || horizon_year > 9000) return fail(nullptr, B200CRON_EINVAL, "horizon_year out of range");
+
+  auto* ctx = new b200cron_ctx();
+  std::string err;
+  if (!build_zone_table(dir, horizon_year, &ctx->zones, &err)) {
+    delete ctx;
+    return fail(nullptr, B200CRON_EINVAL, "zone table: %s", err.c_str());
+  }
+  const HostZoneTable& z = ctx->zones;
+  ctx->devs.resize(ids.size());
+  auto cleanup = [&](int code) { b200cron_ctx_destroy(ctx); return code; };
+  for (size_t i = 0; i < ids.size(); ++i) {
+    Device& d = ctx->devs[i];
+    d.id = ids[i];
+#define CUC(call)                                                                                       \
+  do {                                                                                                  \
+    cudaError_t e_ = (call);                                                                            \
+    if (e_ != cudaSuccess) {                                                                            \
+      fail(nullptr, B200CRON_ECUDA, "%s failed: %s", #call, cudaGetErrorString(e_));                    \
+      return cleanup(B200CRON_ECUDA);                                                                   \
+    }                                                                                                   \
+  } while (0)
+    CUC(cudaSetDevice(d.id));
+    CUC(cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking));
+    for (Slot& s : d.slots) CUC(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+    CUC(cudaMalloc(&d.d_when, z.when.size() * sizeof(int64_t)));
+    CUC(cudaMalloc(&d.d_off, z.off.size() * sizeof(int32_t)));
+    CUC(cudaMalloc(&d.d_zstart, z.zstart.size() * sizeof(int32_t)));
+    CUC(cudaMalloc(&d.d_err, sizeof(int)));
+    CUC(cudaHostAlloc(&d.h_err, sizeof(int), cudaHostAllocDefault));
+    *d.h_err = 0;
+    CUC(cudaMemcpy(d.d_when, z.when.data(), z.when.size() * sizeof(int64_t), cudaMemcpyHostToDevice));
+    CUC(cudaMemcpy(d.d_off, z.off.data(), z.off.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+    CUC(cudaMemcpy(d.d_zstart, z.zstart.data(), z.zstart.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+    CUC(cudaMemset(d.d_err, 0, sizeof(int)));
+#undef CUC
+    d.zt.when = d.d_when;
+    d.zt.off = d.d_off;
+    d.zt.zstart = d.d_zstart;
+    d.zt.nzones = (int32_t)z.names.size();
+    d.zt.horizon = z.horizon;
+  }
+  *out = ctx;
+  return B200CRON_OK;
+}
+
+extern "C" void b200cron_ctx_destroy(b200cron_ctx* ctx) {
+  if (!ctx) return;
+  for (Device& d : ctx->devs) {
+    cudaSetDevice(d.id);
+    for (Slot& s : d.slots) {
+      if (s.stream) { cudaStreamSynchronize(s.stream); cudaStreamDestroy(s.stream); }
+      if (s.buf) cudaFree(s.buf);
+    }
+    if (d.stream) { cudaStreamSynchronize(d.stream); cudaStreamDestroy(d.stream); }
+    if (d.d_when) cudaFree(d.d_when);
+    if (d.d_off) cudaFree(d.d_off);
+    if (d.d_zstart) cudaFree(d.d_zstart);
+    if (d.d_err) cudaFree(d.d_err);
+    if (d.h_err) cudaFreeHost(d.h_err);
+  }
+  delete ctx;
+}
+
+extern "C" const char* b200cron_last_error(const b200cron_ctx* ctx) {
+  return ctx ? ctx->error.c_str() : g_create_error.c_str();
+}
+extern "C" int b200cron_device_count(const b200cron_ctx* ctx) { return ctx ? (int)ctx->devs.size() : 0; }
+extern "C" int b200cron_zone_id(const b200cron_ctx* ctx, const char* name) {
+  if (!ctx || !name) return -1;
+  return ctx->zones.find(name);
+}
+extern "C" int b200cron_zone_count(const b200cron_ctx* ctx) { return ctx ? (int)ctx->zones.names.size() : 0; }
+extern "C" const char* b200cron_zone_name(const b200cron_ctx* ctx, int id) {
+  if (!ctx || id < 0 || id >= (int)ctx->zones.names.size()) return nullptr;
+  return ctx->zones.names[id].c_str();
+}
+extern "C" int b200cron_zone_periods(const b200cron_ctx* ctx, int id, const int64_t** when, const int32_t** off) {
+  if (!ctx || id < 0 || id >= (int)ctx->zones.names.size() || !when || !off) return B200CRON_EINVAL;
+  const int a = ctx->zones.zstart[id], b = ctx->zones.zstart[id + 1];
+  *when = ctx->zones.when.data() + a;
+  *off = ctx->zones.off.data() + a;
+  return b - a;
+}
+extern "C" void* b200cron_host_alloc(size_t bytes) {
+  void* p = nullptr;
+  if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable) != cudaSuccess) return nullptr;
+  return p;
+}
+extern "C" void b200cron_host_free(void* p) {
+  if (p) cudaFreeHost(p);
+}
+extern "C" int b200cron_sync_check(b200cron_ctx* ctx, int dev_index, void* stream) {
+  Device* d = device_at(ctx, dev_index);
+  if (!d) return B200CRON_EINVAL;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  CU(ctx, cudaSetDevice(d->id));
+  cudaStream_t st = stream ? (cudaStream_t)stream : d->stream;
+  CU(ctx, collect_err(*d, st));
+  CU(ctx, cudaStreamSynchronize(st));
+  const int bits = *d->h_err;
+  *d->h_err = 0;
+  if (bits & kErrZone) return fail(ctx, B200CRON_ERANGE, "zone_id outside [0, %d)", (int)ctx->zones.names.size());
+  if (bits & kErrRange)
+    return fail(ctx, B200CRON_ERANGE,
+                "time outside the supported range (years 1..9999; zoned evaluations must stay below year %d)",
+                ctx->zones.horizon_year - 6);
+  return B200CRON_OK;
+}
+extern "C" uint64_t b200cron_launch_count(const b200cron_ctx* ctx) { return ctx ? ctx->launches.load() : 0; }
+
+// =================================================================================================================
+// Next / NextN
+// =================================================================================================================
+extern "C" int b200cron_next_n_dev(b200cron_ctx* ctx, int dev_index, void* stream, const uint64_t* const masks[6],
+                                   const int32_t* zone_id, const int64_t* from, size_t n, int k, int64_t* out) {
+  Device* d = device_at(ctx, dev_index);
+  if (!d) return B200CRON_EINVAL;
+  if (!masks || !from || !out || k < 1 || k > 64) return fail(ctx, B200CRON_EINVAL, "next_n: bad argument (1 <= k <= 64)");
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  CU(ctx, cudaSetDevice(d->id));
+  MaskPlanes m;
+  for (int p = 0; p < 6; ++p) m.p[p] = masks[p];
+  cudaStream_t st = stream ? (cudaStream_t)stream : d->stream;
+  CU(ctx, launch_next(ctx, *d, st, m, zone_id, from, n, k, out));
+  return B200CRON_OK;
+}
+
+extern "C" int b200cron_next_n(b200cron_ctx* ctx, const uint64_t* const masks[6], const int32_t* zone_id,
+                               const int64_t* from, size_t n, int k, int64_t* out) {
+  if (!ctx) return B200CRON_EINVAL;
+  if (!masks || !from || !out || k < 1 || k > 64) return fail(ctx, B200CRON_EINVAL, "next_n: bad argument (1 <= k <= 64)");
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  const int G = (int)ctx->devs.size();
+  // per-chunk staging layout: 6 mask planes | from | out (k per spec) | zone ids
+  const size_t per_spec = 6 * 8 + 8 + (size_t)k * 8 + 4;
+  for (int g = 0; g < G; ++g) {
+    Device& d = ctx->devs[g];
+    const Shard sh = shard_of(n, g, G);
+    if (sh.hi <= sh.lo) continue;
+    CU(ctx, cudaSetDevice(d.id));
+    const size_t len = sh.hi - sh.lo;
+    const size_t chunk = std::min(kChunk, align_up(len, 2));
+    for (Slot& s : d.slots) {
+      int rc = ensure_slot(ctx, s, align_up(chunk, 64) * per_spec + 1024);
+      if (rc) return rc;
+    }
+    int slot = 0;
+    for (size_t c = sh.lo; c < sh.hi; c += chunk, slot = (slot + 1) % kSlots) {
+      Slot& s = d.slots[slot];
+      const size_t cn = std::min(chunk, sh.hi - c);
+      const size_t stride = align_up(chunk, 64);
+      uint64_t* d_masks = reinterpret_cast<uint64_t*>(s.buf);
+      int64_t* d_from = reinterpret_cast<int64_t*>(d_masks + 6 * stride);
+      int64_t* d_out = d_from + stride;
+      int32_t* d_zone = reinterpret_cast<int32_t*>(d_out + stride * k);
+      MaskPlanes m;
+      for (int p = 0; p < 6; ++p) {
+        m.p[p] = d_masks + p * stride;
+        CU(ctx, cudaMemcpyAsync(d_masks + p * stride, masks[p] + c, cn * 8, cudaMemcpyHostToDevice, s.stream));
+      }
+      CU(ctx, cudaMemcpyAsync(d_from, from + c, cn * 8, cudaMemcpyHostToDevice, s.stream));
+      if (zone_id) CU(ctx, cudaMemcpyAsync(d_zone, zone_id + c, cn * 4, cudaMemcpyHostToDevice, s.stream));
+      CU(ctx, launch_next(ctx, d, s.stream, m, zone_id ? d_zone : nullptr, d_from, cn, k, d_out));
+      CU(ctx, cudaMemcpyAsync(out + c * (size_t)k, d_out, cn * (size_t)k * 8, cudaMemcpyDeviceToHost, s.stream));
+    }
+  }
+  for (Device& d : ctx->devs) {
+    CU(ctx, cudaSetDevice(d.id));
+    for (Slot& s : d.slots) CU(ctx, cudaStreamSynchronize(s.stream));
+    CU(ctx, collect_err(d, d.stream));
+    CU(ctx, cudaStreamSynchronize(d.stream));
+  }
+  return check_err_flags(ctx);
+}
+
+// =================================================================================================================
+// unmet_since
+// =================================================================================================================
+extern "C" int b200cron_unmet_since_dev(b200cron_ctx* ctx, int dev_index, void* stream,
+                                        const uint64_t* const masks[6], const int32_t* zone_id,
+                                        const int64_t* earliest, int64_t now, int32_t now_nsec, const uint8_t* policy,
+                                        const uint32_t* active, const uint8_t* flags, const int64_t* deadline,
+                                        size_t n, int64_t* last, int64_t* next, uint32_t* missed, uint8_t* status,
+                                        uint8_t* decision) {
+  Device* d = device_at(ctx, dev_index);
+  if (!d) return B200CRON_EINVAL;
+  if (!masks || !earliest || !last || !next || !missed || !status || !decision)
+    return fail(ctx, B200CRON_EINVAL, "unmet_since: NULL required argument");
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  CU(ctx, cudaSetDevice(d->id));
+  UnmetArgs a{};
+  for (int p = 0; p < 6; ++p) a.m.p[p] = masks[p];
+  a.zone_id = zone_id; a.earliest = earliest; a.now = now; a.now_nsec = now_nsec; a.policy = policy;
+  a.active = active; a.flags = flags; a.deadline = deadline; a.n = n;
+  a.last = last; a.next = next; a.missed = missed; a.status = status; a.decision = decision;
+  CU(ctx, launch_unmet(ctx, *d, stream ? (cudaStream_t)stream : d->stream, a));
+  return B200CRON_OK;
+}
+
+extern "C" int b200cron_unmet_since(b200cron_ctx* ctx, const uint64_t* const masks[6], const int32_t* zone_id,
+                                    const int64_t* earliest, int64_t now, int32_t now_nsec, const uint8_t* policy,
+                                    const uint32_t* active, const uint8_t* flags, const int64_t* deadline, size_t n,
+                                    int64_t* last, int64_t* next, uint32_t* missed, uint8_t* status,
+                                    uint8_t* decision) {
+  if (!ctx) return B200CRON_EINVAL;
+  if (!masks || !earliest || !last || !next || !missed || !status || !decision)
+    return fail(ctx, B200CRON_EINVAL, "unmet_since: NULL required argument");
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  const int G = (int)ctx->devs.size();
+  // staging: 6 planes | earliest | deadline | last | next  (8 B) | zone | active | missed (4 B) | policy flags status decision (1 B)
+  const size_t per_spec = 10 * 8 + 3 * 4 + 4;
+  for (int g = 0; g < G; ++g) {
+    Device& d = ctx->devs[g];
+    const Shard sh = shard_of(n, g, G);
+    if (sh.hi <= sh.lo) continue;
+    CU(ctx, cudaSetDevice(d.id));
+    const size_t len = sh.hi - sh.lo;
+    const size_t chunk = std::min(kChunk, align_up(len, 2));
+    const size_t stride = align_up(chunk, 64);
+    for (Slot& s : d.slots) {
+      int rc = ensure_slot(ctx, s, stride * per_spec + 1024);
+      if (rc) return rc;
+    }
+    int slot = 0;
+    for (size_t c = sh.lo; c < sh.hi; c += chunk, slot = (slot + 1) % kSlots) {
+      Slot& s = d.slots[slot];
+      const size_t cn = std::min(chunk, sh.hi - c);
+      uint64_t* q8 = reinterpret_cast<uint64_t*>(s.buf);
+      uint64_t* d_masks = q8;
+      int64_t* d_earliest = reinterpret_cast<int64_t*>(q8 + 6 * stride);
+      int64_t* d_deadline = d_earliest + stride;
+      int64_t* d_last = d_deadline + stride;
+      int64_t* d_next = d_last + stride;
+      int32_t* q4 = reinterpret_cast<int32_t*>(d_next + stride);
+      int32_t* d_zone = q4;
+      uint32_t* d_active = reinterpret_cast<uint32_t*>(q4 + stride);
+      uint32_t* d_missed = d_active + stride;
+      uint8_t* q1 = reinterpret_cast<uint8_t*>(d_missed + stride);
+      uint8_t* d_policy = q1;
+      uint8_t* d_flags = q1 + stride;
+      uint8_t* d_status = q1 + 2 * stride;
+      uint8_t* d_decision = q1 + 3 * stride;
+      UnmetArgs a{};
+      for (int p = 0; p < 6; ++p) {
+        a.m.p[p] = d_masks + p * stride;
+        CU(ctx, cudaMemcpyAsync(d_masks + p * stride, masks[p] + c, cn * 8, cudaMemcpyHostToDevice, s.stream));
+      }
+      CU(ctx, cudaMemcpyAsync(d_earliest, earliest + c, cn * 8, cudaMemcpyHostToDevice, s.stream));
+      if (deadline) CU(ctx, cudaMemcpyAsync(d_deadline, deadline + c, cn * 8, cudaMemcpyHostToDevice, s.stream));
+      if (zone_id) CU(ctx, cudaMemcpyAsync(d_zone, zone_id + c, cn * 4, cudaMemcpyHostToDevice, s.stream));
+      if (active) CU(ctx, cudaMemcpyAsync(d_active, active + c, cn * 4, cudaMemcpyHostToDevice, s.stream));
+      if (policy) CU(ctx, cudaMemcpyAsync(d_policy, policy + c, cn, cudaMemcpyHostToDevice, s.stream));
+      if (flags) CU(ctx, cudaMemcpyAsync(d_flags, flags + c, cn, cudaMemcpyHostToDevice, s.stream));
+      a.zone_id = zone_id ? d_zone : nullptr;
+      a.earliest = d_earliest; a.now = now; a.now_nsec = now_nsec;
+      a.policy = policy ? d_policy : nullptr; a.active = active ? d_active : nullptr;
+      a.flags = flags ? d_flags : nullptr; a.deadline = deadline ? d_deadline : nullptr;
+      a.n = cn; a.last = d_last; a.next = d_next; a.missed = d_missed; a.status = d_status; a.decision = d_decision;
+      CU(ctx, launch_unmet(ctx, d, s.stream, a));
+      CU(ctx, cudaMemcpyAsync(last + c, d_last, cn * 8, cudaMemcpyDeviceToHost, s.stream));
+      CU(ctx, cudaMemcpyAsync(next + c, d_next, cn * 8, cudaMemcpyDeviceToHost, s.stream));
+      CU(ctx, cudaMemcpyAsync(missed + c, d_missed, cn * 4, cudaMemcpyDeviceToHost, s.stream));
+      CU(ctx, cudaMemcpyAsync(status + c, d_status, cn, cudaMemcpyDeviceToHost, s.stream));
+      CU(ctx, cudaMemcpyAsync(decision + c, d_decision, cn, cudaMemcpyDeviceToHost, s.stream));
+    }
+  }
+  for (Device& d : ctx->devs) {
+    CU(ctx, cudaSetDevice(d.id));
+    for (Slot& s : d.slots) CU(ctx, cudaStreamSynchronize(s.stream));
+    CU(ctx, collect_err(d, d.stream));
+    CU(ctx, cudaStreamSynchronize(d.stream));
+  }
+  return check_err_flags(ctx);
+}
+
+// =================================================================================================================
+// history_prune
+// =================================================================================================================
+extern "C" int b200cron_history_prune_dev(b200cron_ctx* ctx, int dev_index, void* stream, const uint64_t* seg_off,
+                                          const int64_t* key, const int64_t* limit, size_t nseg, size_t nrec,
+                                          uint32_t* perm, uint8_t* keep) {
+  Device* d = device_at(ctx, dev_index);
+  if (!d) return B200CRON_EINVAL;
+  if (!seg_off || (nrec && (!key || !perm || !keep))) return fail(ctx, B200CRON_EINVAL, "history_prune: NULL argument");
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  CU(ctx, cudaSetDevice(d->id));
+  CU(ctx, launch_history(ctx, stream ? (cudaStream_t)stream : d->stream, seg_off, key, limit, nseg, perm, keep));
+  return B200CRON_OK;
+}
+
+extern "C" int b200cron_history_prune(b200cron_ctx* ctx, const uint64_t* seg_off, const int64_t* key,
+                                      const int64_t* limit, size_t nseg, uint32_t* perm, uint8_t* keep) {
+  if (!ctx) return B200CRON_EINVAL;
+  if (!seg_off) return fail(ctx, B200CRON_EINVAL, "history_prune: NULL seg_off");
+  if (nseg == 0) return B200CRON_OK;
+  for (size_t s = 0; s < nseg; ++s)
+    if (seg_off[s + 1] < seg_off[s]) return fail(ctx, B200CRON_EINVAL, "history_prune: seg_off must be non-decreasing");
+  const uint64_t nrec = seg_off[nseg] - seg_off[0];
+  if (nrec && (!key || !perm || !keep)) return fail(ctx, B200CRON_EINVAL, "history_prune: NULL argument");
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  const int G = (int)ctx->devs.size();
+  // Cut on segment boundaries so that records per device balance and no segment straddles two devices.
+  std::vector<size_t> cut(G + 1, nseg);
+  cut[0] = 0;
+  for (int g = 1; g < G; ++g) {
+    const uint64_t target = seg_off[0] + nrec * (uint64_t)g / (uint64_t)G;
+    cut[g] = (size_t)(std::lower_bound(seg_off, seg_off + nseg + 1, target) - seg_off);
+    cut[g] = std::min(std::max(cut[g], cut[g - 1]), nseg);
+  }
+  for (int g = 0; g < G; ++g) {
+    Device& d = ctx->devs[g];
+    const size_t s0 = cut[g], s1 = cut[g + 1];
+    if (s1 <= s0) continue;
+    CU(ctx, cudaSetDevice(d.id));
+    const uint64_t r0 = seg_off[s0], r1 = seg_off[s1];
+    const size_t ns = s1 - s0, nr = (size_t)(r1 - r0);
+    Slot& s = d.slots[0];
+    const size_t a_ns = align_up(ns + 1, 64), a_nr = align_up(nr ? nr : 1, 64);
+    int rc = ensure_slot(ctx, s, a_ns * 16 + a_nr * 13 + 1024);
+    if (rc) return rc;
+    uint64_t* d_off = reinterpret_cast<uint64_t*>(s.buf);
+    int64_t* d_limit = reinterpret_cast<int64_t*>(d_off + a_ns);
+    int64_t* d_key = d_limit + a_ns;
+    uint32_t* d_perm = reinterpret_cast<uint32_t*>(d_key + a_nr);
+    uint8_t* d_keep = reinterpret_cast<uint8_t*>(d_perm + a_nr);
+    CU(ctx, cudaMemcpyAsync(d_off, seg_off + s0, (ns + 1) * 8, cudaMemcpyHostToDevice, s.stream));
+    if (limit) CU(ctx, cudaMemcpyAsync(d_limit, limit + s0, ns * 8, cudaMemcpyHostToDevice, s.stream));
+    if (nr) CU(ctx, cudaMemcpyAsync(d_key, key + r0, nr * 8, cudaMemcpyHostToDevice, s.stream));
+    // the kernel addresses records by absolute offset: bias the record pointers by -r0
+    CU(ctx, launch_history(ctx, s.stream, d_off, d_key - r0, limit ? d_limit : nullptr, ns, d_perm - r0, d_keep - r0));
+    if (nr) {
+      CU(ctx, cudaMemcpyAsync(perm + r0, d_perm, nr * 4, cudaMemcpyDeviceToHost, s.stream));
+      CU(ctx, cudaMemcpyAsync(keep + r0, d_keep, nr, cudaMemcpyDeviceToHost, s.stream));
+    }
+  }
+  for (Device& d : ctx->devs) {
+    CU(ctx, cudaSetDevice(d.id));
+    CU(ctx, cudaStreamSynchronize(d.slots[0].stream));
+  }
+  return B200CRON_OK;
+}

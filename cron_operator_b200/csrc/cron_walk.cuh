@@ -20,9 +20,12 @@
 
 #if defined(__CUDACC__)
 #define CW_HD __host__ __device__ __forceinline__
-#define CW_LDG(p) __ldg(p)
 #else
 #define CW_HD inline
+#endif
+#if defined(__CUDA_ARCH__)
+#define CW_LDG(p) __ldg(p)  // zone table reads go through the read-only path
+#else
 #define CW_LDG(p) (*(p))
 #endif
 

@@ -1,0 +1,288 @@
+// kernels.cuh -- sm_100a kernels of libb200cron.so.  All are HBM-bound integer kernels (no contraction, so no
+// tensor cores): SoA mask planes are read with coalesced 128-bit loads, one lane walks one spec (cron_walk.cuh),
+// and outputs leave through shared-memory staging so that every warp writes full 128-byte lines.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "cron_walk.cuh"
+#include "unmet_walk.cuh"
+
+namespace b200cron {
+
+using cronwalk::kZero;
+using cronwalk::Spec;
+using cronwalk::Walk;
+using cronwalk::ZoneTable;
+
+// supported absolute-time range: years 1..9999 (k8s metav1.Time's RFC 3339 range)
+constexpr int64_t kMinTime = -62135596800LL;
+constexpr int64_t kMaxTime = 253402300799LL;
+constexpr int64_t kSixYears = 6LL * 366 * 86400;
+
+enum : int { kErrRange = 1, kErrZone = 2 };
+
+struct MaskPlanes {
+  const uint64_t* p[6];
+};
+
+__device__ __forceinline__ bool bind_checked(Walk& w, const ZoneTable& zt, int32_t zone, int64_t t, int* err) {
+  if (t < kMinTime || t > kMaxTime) { atomicOr(err, kErrRange); return false; }
+  if (zone == 0) { w.bind_utc(); return true; }
+  if (zone < 0 || zone >= zt.nzones) { atomicOr(err, kErrZone); return false; }
+  w.bind_zone(zt, zone);
+  if (w.zn > 1 && t >= zt.horizon - kSixYears) { atomicOr(err, kErrRange); return false; }
+  return true;
+}
+
+// -------------------------------------------------------------------------------------------------------------
+// next_n: out[i*k + j] = (j+1)-th chained Next() after from[i]              (spec.go Next; cron_controller.go:405,409,436)
+//
+// Layout: each warp owns 64 consecutive specs.  Lane l loads specs (2l, 2l+1) of that tile from each of the 6
+// planes and `from` with one 128-bit load per array (the warp reads 512 contiguous bytes per plane) and walks them
+// one after the other.  k == 1: the two results leave as one 128-bit store.  k > 1: results are staged in the
+// warp's slice of shared memory and written back row-major so that every warp store covers 256 contiguous bytes.
+//   KT = 2,4,8,16,32 (compile-time k): element (row, j) lives at row*KT + ((j + lane_of_row) & (KT-1)); the rotation
+//     spreads the lanes' simultaneous writes of column j over all banks, and the write-back un-rotates for free.
+//   KT = 0 (any other k): transposed staging [j][row] and a division per element on the way out.
+// Algorithmic bytes: 48 (masks) + 8 (from) [+ 4 zone] in, 8k out per spec.
+// -------------------------------------------------------------------------------------------------------------
+constexpr int kNextThreads = 128;
+constexpr int kNextWarpTile = 64;
+constexpr int kNextTile = kNextWarpTile * (kNextThreads / 32);
+
+template <int KT, bool kVec>
+__global__ void __launch_bounds__(kNextThreads)
+next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* __restrict__ from, size_t n, int k_rt,
+              int64_t* __restrict__ out, ZoneTable zt, int* __restrict__ err) {
+  extern __shared__ __align__(16) int64_t stage_all[];  // [warps][64 * k], unused when KT == 1
+  const int k = KT > 0 ? KT : k_rt;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const size_t wbase = (size_t)blockIdx.x * kNextTile + (size_t)warp * kNextWarpTile;
+  if (wbase >= n) return;
+  const size_t i0 = wbase + 2 * (size_t)lane;
+  int64_t* stage = stage_all + (size_t)warp * kNextWarpTile * k;
+
+  uint64_t mk[6][2];
+  int64_t fr[2] = {0, 0};
+  int32_t zz[2] = {0, 0};
+  const bool full = i0 + 1 < n;
+  if (kVec && full) {
+#pragma unroll
+    for (int p = 0; p < 6; ++p) {
+      const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2*>(m.p[p] + i0));
+      mk[p][0] = v.x; mk[p][1] = v.y;
+    }
+    const longlong2 f = __ldg(reinterpret_cast<const longlong2*>(from + i0));
+    fr[0] = f.x; fr[1] = f.y;
+    if (zone_id) {
+      const int2 z = __ldg(reinterpret_cast<const int2*>(zone_id + i0));
+      zz[0] = z.x; zz[1] = z.y;
+    }
+  } else {
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+#pragma unroll
+      for (int p = 0; p < 6; ++p) mk[p][e] = (i0 + e < n) ? __ldg(m.p[p] + i0 + e) : 0;
+      if (i0 + e < n) {
+        fr[e] = __ldg(from + i0 + e);
+        if (zone_id) zz[e] = __ldg(zone_id + i0 + e);
+      }
+    }
+  }
+
+  int64_t ra = kZero, rb = kZero;
+#pragma unroll 1
+  for (int e = 0; e < 2; ++e) {  // one copy of the walk in the instruction stream; operands picked with selects
+    if (i0 + e >= n) break;
+    const Spec s = e ? cronwalk::make_spec(mk[0][1], mk[1][1], mk[2][1], mk[3][1], mk[4][1], mk[5][1])
+                     : cronwalk::make_spec(mk[0][0], mk[1][0], mk[2][0], mk[3][0], mk[4][0], mk[5][0]);
+    Walk w;
+    int64_t t = e ? fr[1] : fr[0];
+    bool ok = bind_checked(w, zt, e ? zz[1] : zz[0], t, err);
+    if (KT == 1) {
+      const int64_t r = ok ? cronwalk::next_from(s, w, t, false) : kZero;
+      if (e) rb = r; else ra = r;
+    } else {
+      bool resident = false;
+      const int row = 2 * lane + e;
+#pragma unroll 1
+      for (int j = 0; j < k; ++j) {
+        if (ok && t != kZero) {
+          t = cronwalk::next_from(s, w, t, resident);
+          resident = true;
+          // chained calls keep walking: re-check the zoned horizon (UTC never trips it)
+          if (t != kZero && w.zn > 1 && t >= zt.horizon - kSixYears) { atomicOr(err, kErrRange); ok = false; t = kZero; }
+        } else {
+          t = kZero;
+        }
+        if (KT > 1) stage[row * KT + ((j + lane) & (KT - 1))] = t;
+        else stage[j * kNextWarpTile + row] = t;
+      }
+    }
+  }
+
+  if (KT == 1) {
+    if (kVec && full) {
+      *reinterpret_cast<longlong2*>(out + i0) = make_longlong2(ra, rb);
+    } else {
+      if (i0 < n) out[i0] = ra;
+      if (i0 + 1 < n) out[i0 + 1] = rb;
+    }
+    return;
+  }
+  __syncwarp();
+  const int rows = (int)((n - wbase) < (size_t)kNextWarpTile ? (n - wbase) : (size_t)kNextWarpTile);
+  int64_t* dst = out + wbase * (size_t)k;
+  if (KT > 1) {
+    constexpr int kRowsPerIter = 32 / (KT > 1 ? KT : 1);
+    const int rr = lane / (KT > 1 ? KT : 1), j = lane % (KT > 1 ? KT : 1);
+    for (int r = rr; r < rows; r += kRowsPerIter)
+      dst[(size_t)r * KT + j] = stage[r * KT + ((j + (r >> 1)) & (KT - 1))];
+  } else {
+    const int words = rows * k;
+    for (int x = lane; x < words; x += 32) {
+      const int r = x / k, j = x - r * k;
+      dst[x] = stage[j * kNextWarpTile + r];
+    }
+  }
+}
+
+// -------------------------------------------------------------------------------------------------------------
+// unmet_since: getNextSchedule + gates + decision per Cron                    (cron_controller.go:163-220, 389-437)
+// One lane per Cron; every array is read and written with lane-consecutive (coalesced) accesses.
+// Algorithmic bytes: 48 + 8 + 4 + 1 + 4 + 1 + 8 = 74 in, 8 + 8 + 4 + 1 + 1 = 22 out per Cron.
+// -------------------------------------------------------------------------------------------------------------
+constexpr int kUnmetThreads = 128;
+
+struct UnmetArgs {
+  MaskPlanes m;
+  const int32_t* zone_id;
+  const int64_t* earliest;
+  int64_t now;
+  int32_t now_nsec;
+  const uint8_t* policy;
+  const uint32_t* active;
+  const uint8_t* flags;
+  const int64_t* deadline;
+  size_t n;
+  int64_t* last;
+  int64_t* next;
+  uint32_t* missed;
+  uint8_t* status;
+  uint8_t* decision;
+};
+
+__global__ void __launch_bounds__(kUnmetThreads) unmet_kernel(UnmetArgs a, ZoneTable zt, int* __restrict__ err) {
+  const size_t i = (size_t)blockIdx.x * kUnmetThreads + threadIdx.x;
+  if (i >= a.n) return;
+  const Spec s = cronwalk::make_spec(__ldg(a.m.p[0] + i), __ldg(a.m.p[1] + i), __ldg(a.m.p[2] + i),
+                                     __ldg(a.m.p[3] + i), __ldg(a.m.p[4] + i), __ldg(a.m.p[5] + i));
+  cronwalk::UnmetIn in;
+  in.earliest = __ldg(a.earliest + i);
+  in.now = a.now;
+  in.now_nsec = a.now_nsec;
+  in.policy = a.policy ? __ldg(a.policy + i) : 0;
+  in.active = a.active ? __ldg(a.active + i) : 0;
+  in.flags = a.flags ? __ldg(a.flags + i) : 0;
+  in.deadline = a.deadline ? __ldg(a.deadline + i) : kZero;
+  int32_t zone = a.zone_id ? __ldg(a.zone_id + i) : 0;
+
+  cronwalk::UnmetOut o;
+  o.last = kZero; o.next = kZero; o.missed = 0; o.status = cronwalk::kStOk; o.decision = 0;
+  bool ok = true;
+  const int64_t lo = in.earliest < in.now ? in.earliest : in.now;
+  if (lo < kMinTime || in.now > kMaxTime || in.earliest > kMaxTime) { atomicOr(err, kErrRange); ok = false; }
+  if (ok && zone != 0) {
+    if (zone < 0 || zone >= zt.nzones) { atomicOr(err, kErrZone); ok = false; }
+    else if (__ldg(zt.zstart + zone + 1) - __ldg(zt.zstart + zone) > 1 && in.now >= zt.horizon - kSixYears) {
+      atomicOr(err, kErrRange); ok = false;
+    }
+  }
+  if (ok) o = cronwalk::unmet_decide(s, zt, zone, in);
+  a.last[i] = o.last;
+  a.next[i] = o.next;
+  a.missed[i] = o.missed;
+  a.status[i] = o.status;
+  a.decision[i] = o.decision;
+}
+
+// -------------------------------------------------------------------------------------------------------------
+// history_prune: stable ascending order of each Cron's finished workloads by creation time + keep/delete flags
+//                                                           (cron_util.go:117-129, cron_controller.go:313-323)
+//
+// A CTA owns kHistSegs consecutive segments, i.e. one contiguous run of records.  The run's keys are brought into
+// shared memory with coalesced loads, every record finds its segment by binary search over the tile's offsets and
+// its stable rank by counting the records of its segment that sort before it (segments are short: the reference
+// keeps historyLimit of them), and perm/keep are staged in shared memory and written back coalesced.
+// Runs longer than kHistCap records are ranked straight from global memory (L2-resident) -- correct for any
+// length, but quadratic in the segment length.
+// Algorithmic bytes: 8 (key) in, 4 (perm) + 1 (keep) out per record; 8 (offset) + 8 (limit) in per segment.
+// -------------------------------------------------------------------------------------------------------------
+constexpr int kHistThreads = 256;
+constexpr int kHistSegs = 256;
+constexpr int kHistCap = 3072;  // records per CTA tile held in shared memory (41 KB static with perm/keep/offsets)
+
+__global__ void __launch_bounds__(kHistThreads)
+history_prune_kernel(const uint64_t* __restrict__ seg_off, const int64_t* __restrict__ key,
+                     const int64_t* __restrict__ limit, size_t nseg, uint32_t* __restrict__ perm,
+                     uint8_t* __restrict__ keep) {
+  __shared__ uint64_t s_off[kHistSegs + 1];
+  __shared__ int64_t s_key[kHistCap];
+  __shared__ uint32_t s_perm[kHistCap];
+  __shared__ uint8_t s_keep[kHistCap];
+  const size_t seg0 = (size_t)blockIdx.x * kHistSegs;
+  const int nsegs = (int)((nseg - seg0) < (size_t)kHistSegs ? (nseg - seg0) : (size_t)kHistSegs);
+  for (int x = threadIdx.x; x <= nsegs; x += kHistThreads) s_off[x] = __ldg(seg_off + seg0 + x);
+  __syncthreads();
+  const uint64_t r0 = s_off[0];
+  const uint64_t total = s_off[nsegs] - r0;
+  const bool in_smem = total <= (uint64_t)kHistCap;
+  if (in_smem) {
+    for (uint32_t x = threadIdx.x; x < total; x += kHistThreads) s_key[x] = __ldg(key + r0 + x);
+    __syncthreads();
+  }
+  for (uint64_t x = threadIdx.x; x < total; x += kHistThreads) {
+    // segment of record x: largest sg with s_off[sg] - r0 <= x
+    int lo = 0, hi = nsegs;
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (s_off[mid] - r0 <= x) lo = mid; else hi = mid;
+    }
+    // (empty segments share an offset with their successor; the search lands on the last of them, which owns x)
+    const uint64_t a = s_off[lo] - r0, b = s_off[lo + 1] - r0;
+    const uint64_t len = b - a;
+    const int64_t kx = in_smem ? s_key[x] : __ldg(key + r0 + x);
+    uint32_t rank = 0;
+    if (in_smem) {
+      for (uint64_t j = a; j < b; ++j) {
+        const int64_t kj = s_key[j];
+        rank += (kj < kx) || (kj == kx && j < x);
+      }
+    } else {
+      for (uint64_t j = a; j < b; ++j) {
+        const int64_t kj = __ldg(key + r0 + j);
+        rank += (kj < kx) || (kj == kx && j < x);
+      }
+    }
+    const int64_t lim = limit ? __ldg(limit + seg0 + lo) : -1;
+    // sorted position `rank` is deleted when rank < len - limit (limit < 0: HistoryLimit nil keeps everything)
+    const uint8_t kp = (lim < 0) ? 1 : !((int64_t)rank < (int64_t)len - lim);
+    if (in_smem) {
+      s_perm[a + rank] = (uint32_t)(x - a);
+      s_keep[a + rank] = kp;
+    } else {
+      perm[r0 + a + rank] = (uint32_t)(x - a);
+      keep[r0 + a + rank] = kp;
+    }
+  }
+  if (in_smem) {
+    __syncthreads();
+    for (uint32_t x = threadIdx.x; x < total; x += kHistThreads) {
+      perm[r0 + x] = s_perm[x];
+      keep[r0 + x] = s_keep[x];
+    }
+  }
+}
+
+}  // namespace b200cron

@@ -1,0 +1,167 @@
+/*
+ * b200cron.h -- C ABI of libb200cron.so: batched cron-schedule evaluation on NVIDIA B200 (sm_100a).
+ *
+ * Drop-in boundary for ONE path of AliyunContainerService/cron-operator: the schedule arithmetic that
+ * internal/controller/cron_controller.go reaches through `cron.Schedule` (robfig/cron/v3 v3.0.1, go.mod:10).
+ * Each entry point cites the reference interface it replaces.  A cgo shim (go/b200cron) binds
+ * exactly these symbols; so do the C++/Python hosts in this repo.
+ *
+ * Conventions
+ *  - All times are int64 Unix seconds.  Go's zero time.Time{} is B200CRON_ZERO_TIME (INT64_MIN).
+ *  - Schedules are robfig SpecSchedule bit masks (bit i = value i allowed, bit 63 = starBit) in SoA form: six
+ *    planes second, minute, hour, dom, month, dow, each `n` uint64.
+ *  - zone_id[i] is the location the schedule is evaluated in: the TZ=/CRON_TZ= location when the spec has one, else
+ *    the id of the process's time.Local (0 = UTC).  NULL means UTC for every spec.  Ids come from b200cron_zone_id.
+ *  - Functions return 0 on success or a negative B200CRON_E* code; b200cron_last_error(ctx) has the text.
+ *  - The caller owns every buffer; the library owns only the context (streams, device staging, zone table).
+ *  - Host-pointer entry points copy H2D/D2H internally (pinned host memory recommended: b200cron_host_alloc) and
+ *    shard `n` contiguously over the context's devices.  `_dev` entry points take device pointers that live on
+ *    device `dev_index` of the context and only enqueue work on `stream` (NULL = the context's stream).
+ *  - Thread-safe per context (one call at a time per context; calls set the CUDA device explicitly).
+ *  - There is no CPU fallback: without a usable GPU b200cron_ctx_create fails.
+ *  - Supported times: years 1..9999 for UTC; zoned evaluations must start below (zone horizon - 6 years), the
+ *    horizon being the year up to which DST footer rules are expanded (default 2200).  Out-of-range elements get
+ *    B200CRON_ZERO_TIME and the call returns B200CRON_ERANGE.
+ */
+#ifndef B200CRON_H
+#define B200CRON_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200CRON_ZERO_TIME INT64_MIN
+
+enum {
+  B200CRON_OK = 0,
+  B200CRON_EINVAL = -1,  /* bad argument */
+  B200CRON_ECUDA = -2,   /* CUDA runtime error (text in last_error) */
+  B200CRON_ERANGE = -3,  /* some element outside the supported time range or with an unknown zone id */
+  B200CRON_EPARSE = -4,  /* b200cron_parse_*: the schedule text is not parsable */
+  B200CRON_ENOMEM = -5
+};
+
+/* per-element status of b200cron_unmet_since (getNextSchedule outcome, cron_controller.go:389-437) */
+enum {
+  B200CRON_ST_OK = 0,
+  B200CRON_ST_UNSCHEDULABLE = 1,     /* Next() hit the zero time: "unschedulable cron" (:410-412) */
+  B200CRON_ST_EARLIEST_AFTER_NOW = 2 /* earliestTime.After(now): only `next` is set (:404-406) */
+};
+/* per-element decision of b200cron_unmet_since (Reconcile, cron_controller.go:163-238) */
+enum {
+  B200CRON_DEC_GATE_DELETED = 1,      /* :163-166 DeletionTimestamp set */
+  B200CRON_DEC_GATE_SUSPENDED = 2,    /* :169-173 */
+  B200CRON_DEC_GATE_DEADLINE = 3,     /* :176-180 now.After(deadline) */
+  B200CRON_DEC_ERR_UNSCHEDULABLE = 4, /* :185-190 error swallowed, no requeue */
+  B200CRON_DEC_REQUEUE_ONLY = 5,      /* :196-199 nothing missed: RequeueAfter = next - now */
+  B200CRON_DEC_SKIP_FORBID = 6,       /* :204-207 */
+  B200CRON_DEC_REPLACE_CREATE = 7,    /* :210-220 delete every active workload, then create */
+  B200CRON_DEC_CREATE = 8             /* :222-238 create the workload named <cron>-<next> */
+};
+enum { B200CRON_POLICY_ALLOW = 0, B200CRON_POLICY_FORBID = 1, B200CRON_POLICY_REPLACE = 2 }; /* api/v1alpha1/cron_types.go:127-139 */
+enum { B200CRON_FLAG_SUSPEND = 1, B200CRON_FLAG_DELETED = 2 };
+
+enum { B200CRON_KIND_SPEC = 0, B200CRON_KIND_EVERY = 1 };
+
+/* robfig/cron v3 spec.go SpecSchedule (the Location is carried separately as a zone name / id) */
+typedef struct b200cron_spec {
+  uint64_t second, minute, hour, dom, month, dow;
+} b200cron_spec;
+
+typedef struct b200cron_ctx b200cron_ctx;
+
+/* ---- host-only: parsing ------------------------------------------------------------------------------------ */
+
+/* Replaces cronv3.ParseStandard(spec) [robfig/cron v3.0.1 parser.go], called at cron_controller.go:392.
+ * 5 fields (minute hour dom month dow), descriptors (@yearly ... @hourly, @every <dur>), optional TZ=/CRON_TZ=
+ * prefix.  On success fills *out, *kind (B200CRON_KIND_*), *every_sec (ConstantDelaySchedule.Delay, seconds) and
+ * `tz` with the prefix's location name ("" when absent, i.e. Location == time.Local).  On failure returns
+ * B200CRON_EPARSE and writes upstream's error text to `err` (the reference wraps it as "unparsable cron %q: %w",
+ * cron_controller.go:394).  Pure host code: needs no context and no GPU. */
+int b200cron_parse_standard(const char* spec, size_t len, b200cron_spec* out, int* kind, int64_t* every_sec,
+                            char* tz, size_t tzcap, char* err, size_t errcap);
+/* Extension (not reachable from the reference, whose parser is 5-field): same grammar with a leading seconds
+ * field, i.e. upstream's cron.NewParser(Second|Minute|Hour|Dom|Month|Dow|Descriptor). */
+int b200cron_parse_with_seconds(const char* spec, size_t len, b200cron_spec* out, int* kind, int64_t* every_sec,
+                                char* tz, size_t tzcap, char* err, size_t errcap);
+
+/* ---- context ----------------------------------------------------------------------------------------------- */
+
+/* Creates a context on `ndev` CUDA devices (ids in `devices`; NULL/0 = current device only) and loads every TZif
+ * zone below `zoneinfo_dir` (NULL = $ZONEINFO or /usr/share/zoneinfo) -- the batched stand-in for
+ * time.LoadLocation, which the reference reaches through ParseStandard's TZ= handling and through time.Local
+ * (charts/cron-operator values.yaml:70-71 `useHostTimezone`).  horizon_year <= 0 selects the default (2200). */
+int b200cron_ctx_create(const int* devices, int ndev, const char* zoneinfo_dir, int horizon_year, b200cron_ctx** out);
+void b200cron_ctx_destroy(b200cron_ctx* ctx);
+const char* b200cron_last_error(const b200cron_ctx* ctx); /* ctx may be NULL: error of the last failed create */
+int b200cron_device_count(const b200cron_ctx* ctx);
+/* zone name -> id usable in zone_id[] (0 for "" and "UTC"); -1 when the name is unknown (LoadLocation error) */
+int b200cron_zone_id(const b200cron_ctx* ctx, const char* name);
+int b200cron_zone_count(const b200cron_ctx* ctx);
+const char* b200cron_zone_name(const b200cron_ctx* ctx, int id);
+/* read-only view of one zone's flattened periods: (*when)[i] <= t < (*when)[i+1] has UTC offset (*off)[i] */
+int b200cron_zone_periods(const b200cron_ctx* ctx, int id, const int64_t** when, const int32_t** off);
+
+/* pinned host memory helpers (cudaHostAlloc / cudaFreeHost); optional but recommended for the host-pointer calls */
+void* b200cron_host_alloc(size_t bytes);
+void b200cron_host_free(void* p);
+
+/* ---- Next / NextN ------------------------------------------------------------------------------------------ */
+
+/* Replaces (*SpecSchedule).Next [robfig/cron v3.0.1 spec.go] as called at cron_controller.go:405,409,436, batched:
+ * out[i*k + j] = the (j+1)-th fire time after from[i] (each the Next() of the previous one), or
+ * B200CRON_ZERO_TIME from the first call that finds no fire time within upstream's 5-year search.
+ * masks[p] points to plane p (n uint64 each). */
+int b200cron_next_n(b200cron_ctx* ctx, const uint64_t* const masks[6], const int32_t* zone_id, const int64_t* from,
+                    size_t n, int k, int64_t* out);
+int b200cron_next_n_dev(b200cron_ctx* ctx, int dev_index, void* stream, const uint64_t* const masks[6],
+                        const int32_t* zone_id, const int64_t* from, size_t n, int k, int64_t* out);
+
+/* ---- unmet-schedule enumeration + concurrency decision -------------------------------------------------------- */
+
+/* Replaces getNextSchedule (cron_controller.go:389-437) and the gates + Allow/Forbid/Replace decision of Reconcile
+ * (:163-220) for n Crons at once.
+ *   earliest[i] = Status.LastScheduleTime ?: CreationTimestamp (:397-402); now/now_nsec = time.Now() split into
+ *   whole seconds and nanoseconds; policy[i] B200CRON_POLICY_*; active[i] = len(activeWorkloads) (:136-151);
+ *   flags[i] B200CRON_FLAG_*; deadline[i] = Spec.Deadline or B200CRON_ZERO_TIME for nil.  policy, active, flags and
+ *   deadline may be NULL (Allow, 0, 0, nil).
+ * Outputs per Cron: last (lastMissed, ZERO when none), next (Next(now)), missed (missedTimes, saturating at
+ * UINT32_MAX; the caller emits TooManyMissedTimes when > 100, :431-434), status, decision.  RequeueAfter is
+ * next - now (:192).  Gated Crons get ZERO times and missed 0. */
+int b200cron_unmet_since(b200cron_ctx* ctx, const uint64_t* const masks[6], const int32_t* zone_id,
+                         const int64_t* earliest, int64_t now, int32_t now_nsec, const uint8_t* policy,
+                         const uint32_t* active, const uint8_t* flags, const int64_t* deadline, size_t n,
+                         int64_t* last, int64_t* next, uint32_t* missed, uint8_t* status, uint8_t* decision);
+int b200cron_unmet_since_dev(b200cron_ctx* ctx, int dev_index, void* stream, const uint64_t* const masks[6],
+                             const int32_t* zone_id, const int64_t* earliest, int64_t now, int32_t now_nsec,
+                             const uint8_t* policy, const uint32_t* active, const uint8_t* flags,
+                             const int64_t* deadline, size_t n, int64_t* last, int64_t* next, uint32_t* missed,
+                             uint8_t* status, uint8_t* decision);
+
+/* ---- finished-history ordering + pruning ---------------------------------------------------------------------- */
+
+/* Replaces sortByCreationTimestamp (cron_util.go:117-129) and the prune index rule of syncCronHistory
+ * (cron_controller.go:313-323) for nseg Crons at once.  Segment s owns records [seg_off[s], seg_off[s+1]) of
+ * key[] (creation timestamps; any int64 key works).  limit[s] = Spec.HistoryLimit, negative = nil (keep all);
+ * limit == NULL keeps all.  Outputs, per record position p inside its segment's sorted order:
+ *   perm[seg_off[s] + p] = index inside the segment of the record that sorts p-th (stable, ascending);
+ *   keep[seg_off[s] + p] = 0 when that record is deleted (p < len - limit), 1 when it stays in Status.History. */
+int b200cron_history_prune(b200cron_ctx* ctx, const uint64_t* seg_off, const int64_t* key, const int64_t* limit,
+                           size_t nseg, uint32_t* perm, uint8_t* keep);
+int b200cron_history_prune_dev(b200cron_ctx* ctx, int dev_index, void* stream, const uint64_t* seg_off,
+                               const int64_t* key, const int64_t* limit, size_t nseg, size_t nrec, uint32_t* perm,
+                               uint8_t* keep);
+
+/* `_dev` calls only enqueue work: this waits for `stream` (NULL = the context's stream) on device dev_index and
+ * reports what the kernels flagged since the last check (B200CRON_ERANGE for out-of-range times / zone ids). */
+int b200cron_sync_check(b200cron_ctx* ctx, int dev_index, void* stream);
+
+/* number of kernels this context has launched so far (bench.py's gpu_launches) */
+uint64_t b200cron_launch_count(const b200cron_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200CRON_H */

@@ -690,8 +690,9 @@ static int go_atoi(const char* s, size_t n, long long* out) {
   unsigned long long v = 0;
   for (; i < n; i++) {
     if (s[i] < '0' || s[i] > '9') return 0;
+    if (v > (1ULL << 63) / 10) return 0; /* would leave the int64 range */
     v = v * 10 + (unsigned)(s[i] - '0');
-    if (v > (1ULL << 63)) return 0; /* out of int64 range */
+    if (v > (1ULL << 63)) return 0;
   }
   if (!neg && v > (unsigned long long)INT64_MAX) return 0;
   *out = neg ? -(long long)v : (long long)v;

@@ -1,0 +1,292 @@
+"""GPU parity tests proper: every call goes through the C ABI of libb200cron.so (cron_operator_b200.api) and is
+compared bit-exactly with the CPU oracle on the same seeded inputs, with the committed golden vectors, and -- at
+full BASELINE sizes -- through size-independent properties."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from cron_operator_b200 import api, synth
+from oracle import pyoracle as po
+
+pytestmark = pytest.mark.gpu
+ts = synth.ts
+V = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "vectors.json")))
+KEYS = ("last", "next", "missed", "status", "decision")
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = api.Context()
+    yield c
+    c.close()
+
+
+@pytest.fixture(scope="module")
+def names(ctx):
+    return ctx.zone_names
+
+
+def _masks_of(texts, with_seconds=False):
+    specs = [api._parse(t, with_seconds) for t in texts]
+    return api.pack_specs(specs)
+
+
+def _dst_zones(ctx, names):
+    return np.array([z for z in range(1, len(names)) if (ctx.zone_periods(z)[0] > ts(2030)).any()])
+
+
+# ---------------------------------------------------------------------------------------------------------------
+def test_golden_vectors(ctx, names):
+    for c in V["next"]:
+        m = np.array([[int(x)] for x in c["masks"]], dtype=np.uint64)
+        z = np.array([names.index(c["zone"])], np.int32)
+        for f, want in zip(c["from"], c["want"]):
+            assert ctx.next_n(m, [f], 4, z)[0].tolist() == want, (c["spec"], c["zone"], f)
+    for c in V["unmet"]:
+        m = np.array([[int(x)] for x in c["masks"]], dtype=np.uint64)
+        z = np.array([names.index(c["zone"])], np.int32)
+        dl = [po.ZERO if c["deadline"] is None else c["deadline"]]
+        got = ctx.unmet_since(m, [c["earliest"]], c["now"], 0, [c["policy"]], [c["active"]], [c["flags"]], dl, z)
+        for k, v in c["want"].items():
+            assert int(got[k][0]) == v, (c["spec"], k)
+    for c in V["history"]:
+        perm, keep = ctx.history_prune([0, len(c["keys"])], np.array(c["keys"], dtype=np.int64),
+                                       [-1 if c["limit"] is None else c["limit"]])
+        assert perm.tolist() == c["perm"] and keep.tolist() == c["keep"]
+
+
+def test_reference_shapes(ctx):
+    """the reference's own known-answer tests, written against the mirrored interface"""
+    now = ts(2026, 1, 1, 12)
+    with pytest.raises(ValueError, match="unparsable cron"):      # K1 cron_controller_test.go:170-186
+        ctx.getNextSchedule("60 31 30 2 *", now - 300, now)
+    with pytest.raises(ValueError, match="unschedulable cron"):   # K2 :188-204
+        ctx.getNextSchedule("0 0 30 2 *", now - 300, now)
+    last, nxt = ctx.getNextSchedule("*/1 * * * *", now - 300, now)  # K3 :206-222
+    assert last == now and nxt == now + 60
+    assert ctx.sortByCreationTimestamp([now - 600, now - 1200, now - 300]).tolist() == [1, 0, 2]  # K4
+    s = api.ParseStandard("CRON_TZ=Asia/Tokyo 0 9 * * *")
+    assert ctx.Next(s, ts(2025, 6, 1)) == ts(2025, 6, 2, 0)
+    assert ctx.Next(api.ParseStandard("@every 1h30m"), 1000) == 1000 + 5400
+    deleted, kept = ctx.syncCronHistory([5, 1, 4, 2, 3], 3)
+    assert deleted.tolist() == [1, 3] and kept.tolist() == [4, 2, 0]
+
+
+def test_C2_full_parity(ctx):
+    """BASELINE config 2: 1M random 5-field UTC specs, next single fire time -- 100% of indices vs the oracle"""
+    n = 1_000_000
+    masks = synth.gen_specs(n)
+    frm = synth.gen_times(n, ts(2024), ts(2034))
+    got = ctx.next_n(masks, frm, 1)
+    want = po.batch_next_n(masks, frm, 1)
+    bad = np.nonzero(got != want)[0]
+    assert len(bad) == 0, (bad[:5], got[bad[:5]], want[bad[:5]])
+    assert 500 < (want == po.ZERO).sum() < 2000
+
+
+def test_C3_shape_parity(ctx, names):
+    """config 3 shape: seconds field, mixed IANA zones incl. DST, next 16 fire times"""
+    n = 400_000
+    masks = synth.gen_specs(n, seed=77, with_seconds=True)
+    zid = synth.gen_zone_ids(n, len(names), _dst_zones(ctx, names), seed=77)
+    frm = synth.gen_times(n, ts(2024), ts(2036), seed=77)
+    # 1%: re-draw to within +-2h of a transition of that spec's zone
+    rng = np.random.default_rng(77)
+    for i in rng.choice(n, n // 100, replace=False):
+        when = ctx.zone_periods(int(zid[i]))[0]
+        w = when[(when > ts(2024)) & (when < ts(2036))]
+        if len(w):
+            frm[i] = int(rng.choice(w)) + int(rng.integers(-7200, 7200))
+    got = ctx.next_n(masks, frm, 16, zid)
+    want = po.batch_next_n(masks, frm, 16, zid, names)
+    bad = np.nonzero((got != want).any(axis=1))[0]
+    assert len(bad) == 0, [(names[zid[b]], int(frm[b]), got[b][:3], want[b][:3]) for b in bad[:3]]
+
+
+@pytest.mark.parametrize("k", [1, 2, 3, 4, 5, 8, 16, 32, 33, 64])
+def test_every_k_and_ragged_n(ctx, names, k):
+    for n in (0, 1, 2, 63, 64, 65, 255, 257, 1001):
+        masks = synth.gen_specs(n, seed=k, with_seconds=True)
+        zid = synth.gen_zone_ids(n, len(names), _dst_zones(ctx, names), seed=k)
+        frm = synth.gen_times(n, ts(2024), ts(2036), seed=k)
+        got = ctx.next_n(masks, frm, k, zid)
+        want = po.batch_next_n(masks, frm, k, zid, names)
+        assert np.array_equal(got, want), (k, n)
+
+
+def test_bad_arguments(ctx):
+    m = synth.gen_specs(4)
+    with pytest.raises(api.B200CronError):
+        ctx.next_n(m, np.zeros(4, np.int64), 0)
+    with pytest.raises(api.B200CronError):
+        ctx.next_n(m, np.zeros(4, np.int64), 65)
+    with pytest.raises(api.B200CronError) as e:
+        ctx.next_n(m, np.array([0, 0, 0, 2**62], np.int64), 1)
+    assert e.value.code == api.ERANGE
+    with pytest.raises(api.B200CronError) as e:
+        ctx.next_n(m, np.zeros(4, np.int64), 1, np.array([0, 1, 2, 100000], np.int32))
+    assert e.value.code == api.ERANGE
+    z = ctx.zone_id("Europe/Berlin")
+    with pytest.raises(api.B200CronError) as e:  # beyond the expanded-footer horizon for a DST zone
+        ctx.next_n(m, np.full(4, ts(2197), np.int64), 1, np.full(4, z, np.int32))
+    assert e.value.code == api.ERANGE
+    assert ctx.next_n(m, np.full(4, ts(2197), np.int64), 1).shape == (4, 1)  # fine in UTC
+    with pytest.raises(api.ParseError):
+        ctx.zone_id("Nope/Nowhere")
+
+
+def test_transitions_through_abi(ctx, names):
+    texts = ["* * * * *", "*/5 * * * *", "30 2 * * *", "0 0 * * *", "0 1 * * *", "59 23 * * *", "0 0 1 * *",
+             "15 3 * * 0", "0 */2 * * *", "30 0 * * *", "45 1-3 25-31 * 0", "0 3 * * *", "*/30 * * * *"]
+    base = _masks_of(texts)
+    for name in ["America/New_York", "Europe/London", "Australia/Lord_Howe", "Africa/Cairo", "America/Havana",
+                 "America/Santiago", "Atlantic/Azores", "Asia/Tehran", "Pacific/Apia", "Asia/Gaza"]:
+        z = names.index(name)
+        when = ctx.zone_periods(z)[0]
+        trans = [int(w) for w in when if ts(2015) < w < ts(2046)]
+        offs = [-1, -61, -3601, -7201, -86401, -40 * 86400, 0, 1, 3600]
+        starts = np.array([t + o for t in trans for o in offs], dtype=np.int64)
+        S, T = len(texts), len(starts)
+        masks = np.ascontiguousarray(np.repeat(base, T, axis=1))
+        frm = np.tile(starts, S)
+        zid = np.full(S * T, z, dtype=np.int32)
+        got = ctx.next_n(masks, frm, 4, zid)
+        want = po.batch_next_n(masks, frm, 4, zid, names)
+        assert np.array_equal(got, want), name
+
+
+def test_device_pointer_path_and_unaligned(ctx, names):
+    import torch
+    n = 100_003
+    masks = synth.gen_specs(n + 1, seed=5, with_seconds=True)
+    zid = synth.gen_zone_ids(n + 1, len(names), _dst_zones(ctx, names), seed=5)
+    frm = synth.gen_times(n + 1, ts(2024), ts(2036), seed=5)
+    dm = torch.from_numpy(masks.view(np.int64)).cuda()
+    dz, df = torch.from_numpy(zid).cuda(), torch.from_numpy(frm).cuda()
+    for shift in (0, 1):  # shift 1: 8-byte-aligned-only pointers -> scalar-load kernel
+        for k in (1, 16):
+            out = torch.empty((n, k), dtype=torch.int64, device="cuda")
+            planes = [dm[p, shift:shift + n] for p in range(6)]
+            ctx.next_n_dev(planes, df[shift:shift + n], out, k, dz[shift:shift + n],
+                           stream=torch.cuda.current_stream().cuda_stream)
+            ctx.sync_check(stream=torch.cuda.current_stream().cuda_stream)
+            want = po.batch_next_n(np.ascontiguousarray(masks[:, shift:shift + n]), frm[shift:shift + n], k,
+                                   zid[shift:shift + n], names)
+            assert np.array_equal(out.cpu().numpy(), want), (shift, k)
+
+
+def _cmp(got, want, ctx_=""):
+    for k in KEYS:
+        bad = np.nonzero(got[k] != want[k])[0]
+        assert len(bad) == 0, (ctx_, k, bad[:5], got[k][bad[:5]], want[k][bad[:5]])
+
+
+def test_unmet_C4_shape(ctx, names):
+    n = 60_000
+    masks = synth.gen_specs(n, seed=41, dense_minutes=0.5)
+    dense = np.array([bin(int(x) & ((1 << 60) - 1)).count("1") for x in masks[1]]) > 6
+    masks[2] = np.where(dense, masks[2] & np.uint64(0x800000000000000E), masks[2])  # keeps the literal oracle affordable
+    masks[2] = np.where(masks[2] & np.uint64(0xFFFFFF), masks[2], np.uint64(1 << 2))
+    zid = synth.gen_zone_ids(n, len(names), _dst_zones(ctx, names), seed=41)
+    now = ts(2026, 3, 29, 12)
+    earliest = now - 30 * 86400 + synth.gen_times(n, -86400, 86400, seed=41)
+    rng = np.random.default_rng(41)
+    policy = rng.integers(0, 3, n).astype(np.uint8)
+    active = rng.choice([0, 1, 2, 3, 4], size=n, p=[0.6, 0.3, 0.04, 0.03, 0.03]).astype(np.uint32)
+    flags = (rng.random(n) < 0.02).astype(np.uint8)
+    deadline = np.where(rng.random(n) < 0.01, now - 100, po.ZERO).astype(np.int64)
+    got = ctx.unmet_since(masks, earliest, now, 0, policy, active, flags, deadline, zid)
+    want = po.batch_unmet(masks, earliest, now, 0, policy, active, flags, deadline, zid, names)
+    _cmp(got, want)
+    assert want["missed"].max() > 100
+    # optional inputs NULL
+    got = ctx.unmet_since(masks[:, :1000].copy(), earliest[:1000], now)
+    want = po.batch_unmet(masks[:, :1000].copy(), earliest[:1000], now)
+    _cmp(got, want)
+
+
+def test_unmet_across_transitions(ctx, names):
+    texts = ["*/20 * * * *", "0 * * * *", "30 2 * * *", "0 0 * * *", "0 1 * * *", "59 23 * * *", "0 0 1 * *",
+             "15 3 * * 0", "0 */2 * * *", "30 0 * * *", "45 1-3 25-31 * 0", "0 3 * * *", "0 0 2 * *", "*/30 0-4 * * *"]
+    base = _masks_of(texts)
+    wins = [(-3 * 86400, 3 * 86400), (-40 * 86400, 1), (-5, 86400 * 2), (-86400, -1), (-7200, 7200), (0, 86400),
+            (-20 * 86400, 20 * 86400), (-3600, 0), (1, 5 * 86400)]
+    for name in ["America/New_York", "Europe/London", "Australia/Lord_Howe", "Africa/Cairo", "America/Havana",
+                 "Atlantic/Azores", "Asia/Tehran", "America/Santiago"]:
+        z = names.index(name)
+        when = ctx.zone_periods(z)[0]
+        for t in [int(w) for w in when if ts(2021) < w < ts(2031)][:10]:
+            for a, b in wins:
+                S = len(texts)
+                zz = np.full(S, z, np.int32)
+                got = ctx.unmet_since(base, np.full(S, t + a), t + b, zone_id=zz)
+                want = po.batch_unmet(base, np.full(S, t + a), t + b, zone_id=zz, zone_names=names)
+                _cmp(got, want, (name, t, a, b))
+
+
+def test_history_parity(ctx):
+    rng = np.random.default_rng(9)
+    for nseg, maxlen in [(1, 3), (1000, 16), (100_000, 16), (257, 40), (3, 5000), (600, 30)]:
+        lens = rng.integers(0, maxlen + 1, nseg)
+        seg_off = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+        key = (1_700_000_000 - rng.integers(0, 400, int(seg_off[-1]))).astype(np.int64)  # many ties
+        for limit in (None, np.full(nseg, 10, np.int64), rng.integers(-1, 20, nseg).astype(np.int64)):
+            perm, keep = ctx.history_prune(seg_off, key, limit)
+            wperm, wkeep = po.batch_history(seg_off, key, limit)
+            assert np.array_equal(perm, wperm) and np.array_equal(keep, wkeep), (nseg, maxlen)
+    perm, keep = ctx.history_prune(np.array([0, 0, 0], np.uint64), np.zeros(0, np.int64), np.array([1, 1], np.int64))
+    assert len(perm) == 0 and len(keep) == 0
+
+
+def test_properties_at_full_size(ctx, names):
+    """size-independent properties on a C3-sized slice (device-resident, no oracle): rows strictly increasing,
+    first > from, chaining (NextN(k) == Next applied k times), determinism across launches"""
+    import torch
+    n, k = 4_000_000, 16
+    masks = synth.gen_specs(n, seed=3, with_seconds=True)
+    zid = synth.gen_zone_ids(n, len(names), _dst_zones(ctx, names), seed=3)
+    frm = synth.gen_times(n, ts(2024), ts(2036), seed=3)
+    dm = torch.from_numpy(masks.view(np.int64)).cuda()
+    dz, df = torch.from_numpy(zid).cuda(), torch.from_numpy(frm).cuda()
+    st = torch.cuda.current_stream().cuda_stream
+    out = torch.empty((n, k), dtype=torch.int64, device="cuda")
+    ctx.next_n_dev(dm, df, out, k, dz, stream=st)
+    ctx.sync_check(stream=st)
+    zero = out == po.ZERO
+    assert bool(((out[:, 1:] > out[:, :-1]) | zero[:, 1:]).all())       # strictly increasing until the zero time
+    assert bool((zero[:, 1:] | ~zero[:, :-1]).all())                    # once zero, always zero
+    assert bool(((out[:, 0] > df) | zero[:, 0]).all())
+    one = torch.empty((n, 1), dtype=torch.int64, device="cuda")
+    cur = df.clone()
+    for j in range(3):                                                   # chaining: column j == Next(column j-1)
+        ok = cur != po.ZERO
+        ctx.next_n_dev(dm, torch.where(ok, cur, torch.zeros_like(cur)), one, 1, dz, stream=st)
+        ctx.sync_check(stream=st)
+        cur = torch.where(ok, one[:, 0], cur)
+        assert bool((cur == out[:, j]).all()), j
+    out2 = torch.empty_like(out)
+    ctx.next_n_dev(dm, df, out2, k, dz, stream=st)
+    ctx.sync_check(stream=st)
+    assert bool((out2 == out).all())
+    # sampled oracle parity on every 997th index
+    idx = np.arange(0, n, 997)
+    want = po.batch_next_n(np.ascontiguousarray(masks[:, idx]), frm[idx], k, zid[idx], names)
+    assert np.array_equal(out[torch.from_numpy(idx).cuda()].cpu().numpy(), want)
+
+
+def test_multi_device_context_matches_single(ctx, names):
+    import torch
+    g = torch.cuda.device_count()
+    if g < 2:
+        pytest.skip("one GPU visible")
+    n = 300_001
+    masks = synth.gen_specs(n, seed=8, with_seconds=True)
+    zid = synth.gen_zone_ids(n, len(names), _dst_zones(ctx, names), seed=8)
+    frm = synth.gen_times(n, ts(2024), ts(2036), seed=8)
+    c2 = api.Context(devices=list(range(g)))
+    try:
+        assert np.array_equal(c2.next_n(masks, frm, 4, zid), ctx.next_n(masks, frm, 4, zid))
+    finally:
+        c2.close()
