@@ -210,7 +210,12 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     ctx = api.Context(devices=[local])
-    st = torch.cuda.current_stream().cuda_stream
+    # a dedicated (non-default) torch stream: the ABI reads stream handle 0 as "the context's own stream", and the
+    # CUDA events below must sit on the stream the kernels are launched on
+    tstream = torch.cuda.Stream()
+    torch.cuda.set_stream(tstream)
+    st = tstream.cuda_stream
+    assert st != 0
     peak, peak_src = peaks()
 
     # this rank's contiguous shard of the synthetic spec list
