@@ -22,7 +22,7 @@ from . import build as _build
 
 ZERO = -(2**63)  # Go's time.Time{} at this boundary (B200CRON_ZERO_TIME)
 OK, EINVAL, ECUDA, ERANGE, EPARSE, ENOMEM = 0, -1, -2, -3, -4, -5
-ST_OK, ST_UNSCHEDULABLE, ST_EARLIEST_AFTER_NOW = 0, 1, 2
+ST_OK, ST_UNSCHEDULABLE, ST_EARLIEST_AFTER_NOW, ST_NONTERMINATING = 0, 1, 2, 3
 (DEC_GATE_DELETED, DEC_GATE_SUSPENDED, DEC_GATE_DEADLINE, DEC_ERR_UNSCHEDULABLE, DEC_REQUEUE_ONLY, DEC_SKIP_FORBID,
  DEC_REPLACE_CREATE, DEC_CREATE) = range(1, 9)
 POLICY = {"Allow": 0, "Forbid": 1, "Replace": 2, "": 0}  # api/v1alpha1/cron_types.go:127-139
@@ -308,7 +308,7 @@ class Context:
         except ParseError as e:
             raise ValueError(f'unparsable cron "{schedule}": {e}') from e
         r = self.UnmetSince([s], [earliest], now)
-        if r["status"][0] == ST_UNSCHEDULABLE:
+        if r["status"][0] in (ST_UNSCHEDULABLE, ST_NONTERMINATING):
             raise ValueError(f'unschedulable cron "{schedule}"')
         return int(r["last"][0]), int(r["next"][0])
 

@@ -39,6 +39,7 @@ struct Device {
   cudaStream_t stream = nullptr;  // default stream of the _dev entry points
   int64_t* d_when = nullptr;
   int32_t* d_off = nullptr;
+  int32_t* d_fpre = nullptr;
   int32_t* d_zstart = nullptr;
   int* d_err = nullptr;
   int* h_err = nullptr;  // pinned mirror
@@ -233,17 +234,20 @@ extern "C" int b200cron_ctx_create(const int* devices, int ndev, const char* zon
     for (Slot& s : d.slots) CUC(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
     CUC(cudaMalloc(&d.d_when, z.when.size() * sizeof(int64_t)));
     CUC(cudaMalloc(&d.d_off, z.off.size() * sizeof(int32_t)));
+    CUC(cudaMalloc(&d.d_fpre, z.fpre.size() * sizeof(int32_t)));
     CUC(cudaMalloc(&d.d_zstart, z.zstart.size() * sizeof(int32_t)));
     CUC(cudaMalloc(&d.d_err, sizeof(int)));
     CUC(cudaHostAlloc(&d.h_err, sizeof(int), cudaHostAllocDefault));
     *d.h_err = 0;
     CUC(cudaMemcpy(d.d_when, z.when.data(), z.when.size() * sizeof(int64_t), cudaMemcpyHostToDevice));
     CUC(cudaMemcpy(d.d_off, z.off.data(), z.off.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+    CUC(cudaMemcpy(d.d_fpre, z.fpre.data(), z.fpre.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
     CUC(cudaMemcpy(d.d_zstart, z.zstart.data(), z.zstart.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
     CUC(cudaMemset(d.d_err, 0, sizeof(int)));
 #undef CUC
     d.zt.when = d.d_when;
     d.zt.off = d.d_off;
+    d.zt.fpre = d.d_fpre;
     d.zt.zstart = d.d_zstart;
     d.zt.nzones = (int32_t)z.names.size();
     d.zt.horizon = z.horizon;
@@ -263,6 +267,7 @@ extern "C" void b200cron_ctx_destroy(b200cron_ctx* ctx) {
     if (d.stream) { cudaStreamSynchronize(d.stream); cudaStreamDestroy(d.stream); }
     if (d.d_when) cudaFree(d.d_when);
     if (d.d_off) cudaFree(d.d_off);
+    if (d.d_fpre) cudaFree(d.d_fpre);
     if (d.d_zstart) cudaFree(d.d_zstart);
     if (d.d_err) cudaFree(d.d_err);
     if (d.h_err) cudaFreeHost(d.h_err);

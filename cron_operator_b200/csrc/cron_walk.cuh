@@ -29,11 +29,16 @@
 #define CW_LDG(p) (*(p))
 #endif
 
+#ifndef CW_TRACE
+#define CW_TRACE(tag, w)
+#endif
+
 namespace cronwalk {
 
 constexpr int64_t kZero = INT64_MIN;  // Go's time.Time{} at every boundary of this library
 constexpr int64_t kAlpha = INT64_MIN;
 constexpr int64_t kOmega = INT64_MAX;
+constexpr int32_t kStuck = 400;  // iterations of one loop entry no terminating upstream walk can reach
 
 // Flattened zone table in HBM (L2-resident: ~0.5 MB for all IANA zones).  Zone z owns entries
 // [zstart[z], zstart[z+1]); entry i is in force for when[i] <= sec < when[i+1] (when of the first entry is kAlpha,
@@ -41,6 +46,7 @@ constexpr int64_t kOmega = INT64_MAX;
 struct ZoneTable {
   const int64_t* when;
   const int32_t* off;
+  const int32_t* fpre;  // per zone: running count of transitions whose gap/overlap contains a local midnight
   const int32_t* zstart;
   int32_t nzones;
   int64_t horizon;  // zoned inputs must be < horizon - 6 years (checked by the caller of the kernels)
@@ -146,6 +152,7 @@ struct Walk {
   // zone
   const int64_t* zw;   // this zone's `when` entries
   const int32_t* zo;   // this zone's offsets
+  const int32_t* zf;   // this zone's midnight-transition prefix counts
   int32_t zn;          // entry count (1 for UTC / fixed zones)
   // cached period holding the last looked-up instant
   int32_t pidx;
@@ -158,11 +165,11 @@ struct Walk {
   int32_t Y, M, D;
 
   CW_HD void bind_utc() {
-    zw = nullptr; zo = nullptr; zn = 1; pidx = 0; off = 0; ps = kAlpha; pe = kOmega;
+    zw = nullptr; zo = nullptr; zf = nullptr; zn = 1; pidx = 0; off = 0; ps = kAlpha; pe = kOmega;
   }
   CW_HD void bind_zone(const ZoneTable& zt, int32_t zone) {
     const int32_t a = CW_LDG(zt.zstart + zone), b = CW_LDG(zt.zstart + zone + 1);
-    zw = zt.when + a; zo = zt.off + a; zn = b - a;
+    zw = zt.when + a; zo = zt.off + a; zf = zt.fpre + a; zn = b - a;
     pidx = -1; off = 0; ps = 1; pe = 0;  // empty cache
     if (zn == 1) { pidx = 0; off = CW_LDG(zo); ps = kAlpha; pe = kOmega; }
   }
@@ -195,11 +202,13 @@ struct Walk {
   CW_HD void load(int64_t tt) {
     t = tt;
     const int64_t l = tt + lookup(tt);
-    int64_t q = l / 86400;
-    int32_t r = (int32_t)(l - q * 86400);
-    if (r < 0) { r += 86400; q -= 1; }
-    dn = (int32_t)q;
-    sod = r;
+    // 86400 = 128 * 675 and |l| < 2^38 inside the supported range (years 1..9999): floor-divide in 32 bits
+    const int32_t hi = (int32_t)(l >> 7);
+    int32_t q = hi / 675;
+    int32_t r = hi - q * 675;
+    if (r < 0) { r += 675; q -= 1; }
+    dn = q;
+    sod = r * 128 + (int32_t)(l & 127);
     civil_from_days(dn, Y, M, D);
   }
 
@@ -261,7 +270,10 @@ CW_HD int64_t walk_next(const Spec& s, Walk& w) {
 
     // ---------------- month loop ----------------
     bool wrapped = false;
+    int32_t guard = 0;
     while (((s.month >> w.M) & 1u) == 0) {
+      CW_TRACE("month", w);
+      if (++guard > kStuck) return kZero;
       if (!added) {
         added = true;
         w.load(w.go_date(w.Y, w.M, 1, 0));
@@ -288,7 +300,14 @@ CW_HD int64_t walk_next(const Spec& s, Walk& w) {
     if (wrapped) continue;
 
     // ---------------- day loop ----------------
+    // Upstream bug guard: in zones that skipped a whole calendar day (Kiritimati 1994-12-31, Apia 2011-12-30, ...)
+    // AddDate(0,0,1) from the day before resolves back to the same instant and upstream's day loop never returns.
+    // A terminating day loop wraps at Day()==1 within 31 (+ a few DST-fix) steps; beyond kStuck we report the zero
+    // time ("unschedulable"), as the oracle does.
+    guard = 0;
     while (!day_matches(s, w.D, w.dn)) {
+      CW_TRACE("day", w);
+      if (++guard > kStuck) return kZero;
       if (!added) {
         added = true;
         w.load(w.go_date(w.Y, w.M, w.D, 0));
@@ -320,7 +339,10 @@ CW_HD int64_t walk_next(const Spec& s, Walk& w) {
     if (wrapped) continue;
 
     // ---------------- hour loop ----------------
+    guard = 0;
     while (((s.hour >> w.hour()) & 1u) == 0) {
+      CW_TRACE("hour", w);
+      if (++guard > kStuck) return kZero;
       if (!added) {
         added = true;
         w.load(w.go_date(w.Y, w.M, w.D, w.hour() * 3600));
@@ -341,7 +363,10 @@ CW_HD int64_t walk_next(const Spec& s, Walk& w) {
     if (wrapped) continue;
 
     // ---------------- minute loop ----------------
+    guard = 0;
     while (((s.minute >> w.minute()) & 1ULL) == 0) {
+      CW_TRACE("minute", w);
+      if (++guard > kStuck) return kZero;
       if (!added) {
         added = true;
         // Truncate(time.Minute) works on absolute time; the zero Time is a multiple of 60 s away from 1970
@@ -365,7 +390,10 @@ CW_HD int64_t walk_next(const Spec& s, Walk& w) {
     if (wrapped) continue;
 
     // ---------------- second loop ----------------
+    guard = 0;
     while (((s.second >> w.second()) & 1ULL) == 0) {
+      CW_TRACE("second", w);
+      if (++guard > kStuck) return kZero;
       added = true;  // Truncate(time.Second) is the identity on whole seconds
       const int32_t sc = w.second();
       const uint64_t later = s.second & ~((2ULL << sc) - 1ULL);
@@ -386,6 +414,113 @@ CW_HD int64_t walk_next(const Spec& s, Walk& w) {
   }
 }
 
+
+// first matching time of day >= (h, mi, sc), or -1
+CW_HD int32_t next_tod_ge(const Spec& s, int32_t h, int32_t mi, int32_t sc) {
+  if ((s.hour >> h) & 1u) {
+    if ((s.minute >> mi) & 1ULL) {
+      const uint64_t m = s.second >> sc;
+      if (m) return h * 3600 + mi * 60 + sc + ctz64(m);
+    }
+    const uint64_t m = s.minute & ~((2ULL << mi) - 1ULL);
+    if (m) return h * 3600 + ctz64(m) * 60 + ctz64(s.second);
+  }
+  const uint32_t hm = s.hour & ~((2u << h) - 1u);
+  if (hm) return ctz32(hm) * 3600 + ctz64(s.minute) * 60 + ctz64(s.second);
+  return -1;
+}
+
+// Closed-form Next() from the resident state (t = input + 1s).  Returns true and leaves `w` on the result (or sets
+// *out = kZero) when the answer is provably what upstream's walk produces; returns false -- with w's fields (not
+// its period cache) untouched -- when only the step emulation (walk_next) can tell.
+//
+// Upstream's walk equals "the smallest instant >= t whose local fields match" whenever (1) every Date() call it
+// makes resolves naturally and (2) its Add-based hour/minute/second loops never step across a zone transition.
+// Date() targets are: the hour start of t (hour reset), the midnight of t's day or the 1st of t's month (day /
+// month reset), every midnight up to the fire day, and the 1st of skipped months -- all local midnights except the
+// first.  A local midnight is natural unless it lies in the gap/overlap of a transition; those transitions are
+// counted in the zone table (fpre), so "none between here and the fire day" is two loads.  Add-based loops run on
+// t's own day (until the fire, or until the Hour()==0 wrap at the next midnight) and on the fire day from its
+// midnight: both stretches must sit inside one period.  Offsets must be whole minutes (Truncate is absolute).
+CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
+  const int32_t sod = w.sod;
+  const int32_t h = sod / 3600, mi = (sod - h * 3600) / 60, sc = sod - h * 3600 - mi * 60;
+  const bool zoned = w.zn > 1;
+  if (zoned) {
+    if (w.off % 60 != 0) return false;
+    if (!w.natural((int64_t)w.dn * 86400 + h * 3600)) return false;  // hour reset Date(Y,M,D,h,0,0)
+  }
+  const bool today = ((s.month >> w.M) & 1u) && day_matches(s, w.D, w.dn);
+  if (today) {
+    const int32_t tod = next_tod_ge(s, h, mi, sc);
+    if (tod >= 0) {
+      const int64_t r = w.t + (tod - sod);
+      if (r >= w.pe) return false;
+      w.t = r;
+      w.sod = tod;
+      *out = r;
+      return true;
+    }
+    if (w.t + (86400 - sod) >= w.pe) return false;  // the wrap at the next local midnight must happen in this period
+  }
+  // ---- calendar search for the next matching day after today ----
+  const int32_t year_limit = w.Y + 5;
+  int32_t Yc = w.Y, Mc = w.M, Dc = 0;
+  int32_t first_dn = w.dn - (w.D - 1);
+  bool found = false;
+  if ((s.month >> Mc) & 1u) {
+    const uint32_t dm = month_daymask(s, Yc, Mc, first_dn) & ~((2u << w.D) - 1u);
+    if (dm) { Dc = ctz32(dm); found = true; }
+  }
+  while (!found) {
+    const uint32_t later = s.month & ~((2u << Mc) - 1u);
+    if (later) { Mc = ctz32(later); } else { ++Yc; Mc = ctz32(s.month); }
+    if (Yc > year_limit) break;
+    first_dn = days_from_civil(Yc, Mc, 1);
+    const uint32_t dm = month_daymask(s, Yc, Mc, first_dn);
+    if (dm) { Dc = ctz32(dm); found = true; }
+  }
+  const int32_t found_dn = found ? first_dn + Dc - 1 : days_from_civil(year_limit + 1, 1, 1);
+  const int64_t x_mid = (int64_t)found_dn * 86400;  // local midnight of the fire day (or of the limit's Jan 1)
+  const int32_t tod1 = ctz32(s.hour) * 3600 + ctz64(s.minute) * 60 + ctz64(s.second);
+  if (!zoned) {
+    if (!found) { *out = kZero; return true; }
+    w.t = x_mid + tod1 - w.off;
+    w.dn = found_dn; w.sod = tod1; w.Y = Yc; w.M = Mc; w.D = Dc;
+    *out = w.t;
+    return true;
+  }
+  // ---- zoned: are all the midnights natural, and is the fire day's stretch inside one period? ----
+  const int32_t total_flagged = CW_LDG(w.zf + (w.zn - 1));
+  int32_t i_lo = 0;
+  if (total_flagged != 0) {
+    // earliest Date() target: the 1st of t's month when the month is reset, else today's midnight
+    const int64_t x_lo = (int64_t)(((s.month >> w.M) & 1u) ? w.dn : (w.dn - (w.D - 1))) * 86400;
+    w.lookup(x_lo - w.off - 2 * 86400);
+    i_lo = w.pidx;
+  }
+  int32_t o = w.lookup(x_mid);
+  if (o != 0) {
+    const int32_t o2 = w.lookup(x_mid - o);
+    if (o2 != o) return false;
+  }
+  const int64_t u_mid = x_mid - o;  // Date(found day, 00:00:00); the cache now holds its period
+  if (u_mid < w.ps || u_mid >= w.pe) return false;
+  if (total_flagged != 0) {
+    // transitions strictly after i_lo up to the one that ends the fire day's period
+    const int32_t i_hi = (w.pidx + 1 < w.zn) ? w.pidx + 1 : w.pidx;
+    if (CW_LDG(w.zf + i_hi) != CW_LDG(w.zf + i_lo)) return false;
+  }
+  if (!found) { *out = kZero; return true; }
+  if (o % 60 != 0) return false;
+  const int64_t r = u_mid + tod1;
+  if (r >= w.pe) return false;
+  w.t = r;
+  w.dn = found_dn; w.sod = tod1; w.Y = Yc; w.M = Mc; w.D = Dc;
+  *out = r;
+  return true;
+}
+
 // Next(t): t.Add(1s) then the walk.  `resident` = w already holds the fields of `t` (chained NextN calls).
 CW_HD int64_t next_from(const Spec& s, Walk& w, int64_t t, bool resident) {
   const int64_t t1 = t + 1;
@@ -395,6 +530,10 @@ CW_HD int64_t next_from(const Spec& s, Walk& w, int64_t t, bool resident) {
   } else {
     w.load(t1);
   }
+  if (s.never) return kZero;
+  int64_t r;
+  if (fast_next(s, w, &r)) return r;
+  w.lookup(w.t);  // fast_next may have moved the period cache; the step emulation wants it on t
   return walk_next(s, w);
 }
 

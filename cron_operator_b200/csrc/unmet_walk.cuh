@@ -10,7 +10,7 @@
 
 namespace cronwalk {
 
-enum : uint8_t { kStOk = 0, kStUnschedulable = 1, kStEarliestAfterNow = 2 };
+enum : uint8_t { kStOk = 0, kStUnschedulable = 1, kStEarliestAfterNow = 2, kStNonTerminating = 3 };
 enum : uint8_t {
   kDecGateDeleted = 1,       // cron_controller.go:163-166
   kDecGateSuspended = 2,     // :169-173
@@ -191,6 +191,13 @@ CW_HD UnmetOut unmet_decide(const Spec& s, const ZoneTable& zt, int32_t zone, co
     return o;
   }
   // :409  for t := sched.Next(earliest); !t.After(now); t = sched.Next(t)
+  //
+  // Upstream bug guard: across a DST overlap a chained Next() can return a time at or before its argument (e.g.
+  // Pacific/Chatham: a fire found at 02:59 on the repeated hour makes the next call reset to 02:00 and come back to
+  // the first 03:00), and then upstream's loop above cycles forever.  Next() is a pure function of t, so the loop
+  // is in a cycle exactly when it revisits a fire time: after every backward step the largest origin is remembered
+  // and a fire equal to it ends the call with kStNonTerminating instead of hanging.  No other input is affected.
+  int64_t anchor = kZero;
   int64_t t = next_from(s, w, in.earliest, false);
   while (t == kZero || t <= in.now) {
     if (t == kZero) {  // :410-412
@@ -198,9 +205,15 @@ CW_HD UnmetOut unmet_decide(const Spec& s, const ZoneTable& zt, int32_t zone, co
       return o;
     }
     o.missed = sat_add(o.missed, 1);
-    chain_fast_forward(s, w, in.now, &o.missed);
+    if (anchor == kZero || w.t > anchor) chain_fast_forward(s, w, in.now, &o.missed);
     o.last = w.t;
-    t = next_from(s, w, w.t, true);
+    const int64_t prev = w.t;
+    t = next_from(s, w, prev, true);
+    if (t != kZero && t <= prev && prev > anchor) anchor = prev;
+    if (anchor != kZero && t == anchor) {
+      o.last = kZero; o.missed = 0; o.status = kStNonTerminating; o.decision = kDecErrUnschedulable;
+      return o;
+    }
   }
   o.next = next_from(s, w, in.now, false);  // :436
   if (o.last == kZero) o.decision = kDecRequeueOnly;                                        // :196-199

@@ -401,6 +401,7 @@ bool build_zone_table(const std::string& zoneinfo_dir, int horizon_year, HostZon
   out->zstart.push_back(0);
   out->when.push_back(kAlpha);
   out->off.push_back(0);
+  out->fpre.push_back(0);
   std::vector<uint8_t> data;
   for (const std::string& rel : files) {
     if (rel == "UTC") continue;  // id 0
@@ -413,6 +414,17 @@ bool build_zone_table(const std::string& zoneinfo_dir, int horizon_year, HostZon
     flatten(z, horizon_year, &w, &o);
     out->when.insert(out->when.end(), w.begin(), w.end());
     out->off.insert(out->off.end(), o.begin(), o.end());
+    // A transition at T from offset A to B makes the local times [T+min(A,B), T+max(A,B)] missing (gap) or double
+    // (overlap); flag it when a local midnight falls in that closed interval.
+    int32_t run = 0;
+    for (size_t i = 0; i < w.size(); ++i) {
+      if (i > 0) {
+        const int64_t lo = w[i] + std::min(o[i - 1], o[i]), hi = w[i] + std::max(o[i - 1], o[i]);
+        const int64_t first_mid = floordiv(lo + kDay - 1, kDay) * kDay;  // first multiple of a day >= lo
+        if (first_mid <= hi) ++run;
+      }
+      out->fpre.push_back(run);
+    }
   }
   out->zstart.push_back((int32_t)out->when.size());
   if (out->names.size() <= 1) {

@@ -17,6 +17,9 @@ struct HostZoneTable {
   std::vector<int32_t> zstart;     // names.size() + 1 entries
   std::vector<int64_t> when;       // first entry of every zone is INT64_MIN
   std::vector<int32_t> off;
+  // fpre[i] (zone-relative prefix): number of transitions among this zone's entries 1..i whose gap or overlap
+  // contains a local midnight -- the only transitions at which Date(y, m, d, 0, 0, 0) is not "natural"
+  std::vector<int32_t> fpre;
   int64_t horizon = 0;             // unix second up to which footer rules were expanded
   int horizon_year = 0;
 

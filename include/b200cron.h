@@ -47,7 +47,9 @@ enum {
 enum {
   B200CRON_ST_OK = 0,
   B200CRON_ST_UNSCHEDULABLE = 1,     /* Next() hit the zero time: "unschedulable cron" (:410-412) */
-  B200CRON_ST_EARLIEST_AFTER_NOW = 2 /* earliestTime.After(now): only `next` is set (:404-406) */
+  B200CRON_ST_EARLIEST_AFTER_NOW = 2, /* earliestTime.After(now): only `next` is set (:404-406) */
+  B200CRON_ST_NONTERMINATING = 3      /* upstream's loop :409 would cycle forever (chained Next() went backwards across a
+                                         DST overlap); reported with decision ERR_UNSCHEDULABLE instead of hanging */
 };
 /* per-element decision of b200cron_unmet_since (Reconcile, cron_controller.go:163-238) */
 enum {

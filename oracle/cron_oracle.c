@@ -559,8 +559,16 @@ static int day_matches(const orc_spec* s, const civil* c) {
   return dom_match || dow_match;
 }
 
+/* DELIBERATE DIVERGENCE FROM UPSTREAM (the only one): in zones that skipped a whole calendar day (Pacific/Kiritimati
+ * 1994-12-31, Pacific/Apia 2011-12-30, ...) AddDate(0,0,1) from the day before resolves back to the same instant, so
+ * upstream's `for !dayMatches(s, t)` loop never terminates -- real Go hangs.  A terminating loop entry needs at most
+ * 31 (+ a few DST-fix) day steps, 12 month steps, 25 hour steps, 61 minute or second steps before it exits or wraps;
+ * past ORC_STUCK iterations of one loop entry the restatement returns the zero time ("unschedulable cron"). */
+#define ORC_STUCK 400
+
 int64_t orc_spec_next(const orc_spec* s, const orc_loc* loc, int64_t t) {
   g_steps = 0;
+  int guard;
   /* origLocation / s.Location handling: at this boundary every time is an absolute unix second and `loc` is the
    * effective location (s.Location, or t.Location() when s.Location == time.Local), so In()/In(orig) are no-ops. */
   t = t + 1; /* t.Add(1s - t.Nanosecond()) with whole-second inputs */
@@ -572,8 +580,10 @@ WRAP:
   c = fields_of(loc, t);
   if (c.year > year_limit) return ORC_ZERO;
 
+  guard = 0;
   while (((1ULL << (unsigned)c.month) & s->month) == 0) {
     g_steps++;
+    if (++guard > ORC_STUCK) return ORC_ZERO;
     if (!added) {
       added = 1;
       t = orc_go_date(c.year, c.month, 1, 0, 0, 0, loc);
@@ -583,8 +593,10 @@ WRAP:
     if (c.month == 1) goto WRAP;
   }
 
+  guard = 0;
   while (!day_matches(s, &c)) {
     g_steps++;
+    if (++guard > ORC_STUCK) return ORC_ZERO;
     if (!added) {
       added = 1;
       t = orc_go_date(c.year, c.month, c.day, 0, 0, 0, loc);
@@ -602,8 +614,10 @@ WRAP:
     if (c.day == 1) goto WRAP;
   }
 
+  guard = 0;
   while (((1ULL << (unsigned)c.hour) & s->hour) == 0) {
     g_steps++;
+    if (++guard > ORC_STUCK) return ORC_ZERO;
     if (!added) {
       added = 1;
       t = orc_go_date(c.year, c.month, c.day, c.hour, 0, 0, loc);
@@ -613,8 +627,10 @@ WRAP:
     if (c.hour == 0) goto WRAP;
   }
 
+  guard = 0;
   while (((1ULL << (unsigned)c.minute) & s->minute) == 0) {
     g_steps++;
+    if (++guard > ORC_STUCK) return ORC_ZERO;
     if (!added) {
       added = 1;
       t = t - fmod_(t, 60); /* Truncate(time.Minute): absolute, since the zero Time is a multiple of 60 s from 1970 */
@@ -624,8 +640,10 @@ WRAP:
     if (c.minute == 0) goto WRAP;
   }
 
+  guard = 0;
   while (((1ULL << (unsigned)c.second) & s->second) == 0) {
     g_steps++;
+    if (++guard > ORC_STUCK) return ORC_ZERO;
     if (!added) {
       added = 1; /* Truncate(time.Second) is the identity on whole seconds */
     }
@@ -996,11 +1014,23 @@ int orc_get_next_schedule(const orc_spec* s, const orc_loc* loc, int64_t earlies
   }
   uint64_t missed_times = 0;
   int64_t last = ORC_ZERO;
-  /* :409  for t := sched.Next(earliest); !t.After(now); t = sched.Next(t)   (zero time is "not after now") */
-  for (int64_t t = orc_spec_next(s, loc, earliest); t == ORC_ZERO || t <= now; t = orc_spec_next(s, loc, t)) {
+  /* :409  for t := sched.Next(earliest); !t.After(now); t = sched.Next(t)   (zero time is "not after now")
+   *
+   * DELIBERATE DIVERGENCE (second and last): across a DST overlap a chained Next() can return a time at or before
+   * its argument (Pacific/Chatham: a fire found at 02:59 on the repeated hour makes the next call reset to 02:00 and
+   * return the first 03:00 again) and upstream's loop then cycles forever.  Next() is a pure function of t, so the
+   * loop is in a cycle exactly when it revisits a fire time: after each backward step the largest origin is kept and
+   * a fire equal to it ends the call with ORC_ST_NONTERMINATING. */
+  int64_t anchor = ORC_ZERO;
+  int64_t t = orc_spec_next(s, loc, earliest);
+  while (t == ORC_ZERO || t <= now) {
     if (t == ORC_ZERO) return ORC_ST_UNSCHEDULABLE; /* :410-412 */
     last = t;
     missed_times++;
+    int64_t tn = orc_spec_next(s, loc, t);
+    if (tn != ORC_ZERO && tn <= t && t > anchor) anchor = t;
+    if (anchor != ORC_ZERO && tn == anchor) return ORC_ST_NONTERMINATING;
+    t = tn;
   }
   *last_missed = last;
   *missed = missed_times;
@@ -1022,7 +1052,7 @@ int orc_reconcile_decide(const orc_spec* s, const orc_loc* loc, int64_t earliest
   if (deadline != ORC_ZERO && (now > deadline || (now == deadline && now_nsec > 0))) return ORC_DEC_GATE_DEADLINE;
   int st = orc_get_next_schedule(s, loc, earliest, now, last_missed, next, missed);
   *status = (uint8_t)st;
-  if (st == ORC_ST_UNSCHEDULABLE) return ORC_DEC_ERR_UNSCHEDULABLE;      /* :185-190 */
+  if (st == ORC_ST_UNSCHEDULABLE || st == ORC_ST_NONTERMINATING) return ORC_DEC_ERR_UNSCHEDULABLE; /* :185-190 */
   if (*last_missed == ORC_ZERO) return ORC_DEC_REQUEUE_ONLY;             /* :196-199 */
   if (policy == ORC_POLICY_FORBID && active > 0) return ORC_DEC_SKIP_FORBID; /* :204-207 */
   if (policy == ORC_POLICY_REPLACE) return ORC_DEC_REPLACE_CREATE;       /* :210-220 */

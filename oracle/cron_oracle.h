@@ -65,8 +65,9 @@ int64_t orc_spec_next(const orc_spec* s, const orc_loc* loc, int64_t t);
 int64_t orc_last_steps(void);
 
 /* getNextSchedule (cron_controller.go:389-437) on an already-parsed spec.
- * status: 0 ok, 1 "unschedulable cron" error, 2 earliest.After(now) early return. */
-enum { ORC_ST_OK = 0, ORC_ST_UNSCHEDULABLE = 1, ORC_ST_EARLIEST_AFTER_NOW = 2 };
+ * status: 0 ok, 1 "unschedulable cron" error, 2 earliest.After(now) early return, 3 upstream's loop would never
+ * terminate (time went backwards across a DST overlap; see cron_oracle.c). */
+enum { ORC_ST_OK = 0, ORC_ST_UNSCHEDULABLE = 1, ORC_ST_EARLIEST_AFTER_NOW = 2, ORC_ST_NONTERMINATING = 3 };
 int orc_get_next_schedule(const orc_spec* s, const orc_loc* loc, int64_t earliest, int64_t now,
                           int64_t* last_missed, int64_t* next, uint64_t* missed);
 

@@ -17,7 +17,7 @@ _LIB = None
 ZERO = -(2**63)  # Go's time.Time{} at this repo's boundaries
 ZONEINFO_DIR = os.environ.get("ZONEINFO", "/usr/share/zoneinfo")
 
-ST_OK, ST_UNSCHEDULABLE, ST_EARLIEST_AFTER_NOW = 0, 1, 2
+ST_OK, ST_UNSCHEDULABLE, ST_EARLIEST_AFTER_NOW, ST_NONTERMINATING = 0, 1, 2, 3
 (DEC_GATE_DELETED, DEC_GATE_SUSPENDED, DEC_GATE_DEADLINE, DEC_ERR_UNSCHEDULABLE, DEC_REQUEUE_ONLY,
  DEC_SKIP_FORBID, DEC_REPLACE_CREATE, DEC_CREATE) = range(1, 9)
 

@@ -41,6 +41,7 @@ static ZoneTable view(void* t) {
   ZoneTable z;
   z.when = h->when.data();
   z.off = h->off.data();
+  z.fpre = h->fpre.data();
   z.zstart = h->zstart.data();
   z.nzones = (int32_t)h->names.size();
   z.horizon = h->horizon;

@@ -144,3 +144,23 @@ def test_unmet_C4_shape_mixed_zones():
     got = shim.unmet(masks, earliest, now, 0, policy, active, flags, deadline, zone_id=zid)
     want = po.batch_unmet(masks, earliest, now, 0, policy, active, flags, deadline, zone_id=zid, zone_names=NAMES)
     _cmp(got, want)
+
+
+def test_upstream_hangs_are_reported_not_reproduced():
+    """Two inputs on which upstream never returns (both found by tests/stress_walk.py); oracle and kernels agree on a
+    terminating answer (DESIGN.md 'Deliberate divergences')."""
+    # (1) robfig day loop: Kiritimati skipped 1994-12-31, AddDate(0,0,1) from Dec 30 resolves back to Dec 30
+    z = NAMES.index("Pacific/Kiritimati")
+    m = np.array([[0x1], [0x8FFFFFFFFFFFFFFF], [0x8000000000FFFFFF], [0x2AAAAAA], [0x8000000000001FFE], [0x49]],
+                 dtype=np.uint64)
+    got = shim.next_n(m, np.array([788858203]), 3, np.array([z], np.int32))
+    want = po.batch_next_n(m, np.array([788858203]), 3, np.array([z], np.int32), NAMES)
+    assert np.array_equal(got, want) and got[0, 0] == po.ZERO
+    # (2) getNextSchedule loop: Chatham's repeated 02:45-03:45 hour sends a chained Next() back to the first 03:00
+    z = NAMES.index("Pacific/Chatham")
+    m = np.array([[0x1], [0x800010000100001], [0x8], [0x80000000FFFFFFFE], [0x8000000000001FFE], [0x11]], dtype=np.uint64)
+    zz = np.array([z], np.int32)
+    got = shim.unmet(m, np.array([1838162695]), 1839851648, zone_id=zz)
+    want = po.batch_unmet(m, np.array([1838162695]), 1839851648, zone_id=zz, zone_names=NAMES)
+    _cmp(got, want)
+    assert got["status"][0] == po.ST_NONTERMINATING and got["decision"][0] == po.DEC_ERR_UNSCHEDULABLE
