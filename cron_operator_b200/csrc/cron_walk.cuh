@@ -57,7 +57,13 @@ struct Spec {  // sanitised masks: only the bits upstream can test are kept
   uint32_t hour, dom, month, dow;
   bool star;   // Dom&starBit || Dow&starBit  -> AND rule, else OR rule (spec.go dayMatches)
   bool never;  // some field can never match: upstream walks to the 5-year limit and returns the zero time
+  int32_t tod1;     // first matching second of day (first hour, first minute, first second); valid when !never
+  int32_t first_ms; // first matching minute * 60 + first matching second
+  int32_t first_s;  // first matching second
 };
+
+CW_HD int ctz32(uint32_t x);
+CW_HD int ctz64(uint64_t x);
 
 CW_HD Spec make_spec(uint64_t second, uint64_t minute, uint64_t hour, uint64_t dom, uint64_t month, uint64_t dow) {
   Spec s;
@@ -70,6 +76,9 @@ CW_HD Spec make_spec(uint64_t second, uint64_t minute, uint64_t hour, uint64_t d
   s.star = ((dom | dow) >> 63) != 0;
   const bool no_day = s.star ? (s.dom == 0 || s.dow == 0) : (s.dom == 0 && s.dow == 0);
   s.never = s.second == 0 || s.minute == 0 || s.hour == 0 || s.month == 0 || no_day;
+  s.first_s = ctz64(s.second | (1ULL << 60));
+  s.first_ms = ctz64(s.minute | (1ULL << 60)) * 60 + s.first_s;
+  s.tod1 = ctz32(s.hour | (1u << 24)) * 3600 + s.first_ms;
   return s;
 }
 
@@ -83,7 +92,8 @@ CW_HD int ctz32(uint32_t x) {
 }
 CW_HD int ctz64(uint64_t x) {
 #if defined(__CUDA_ARCH__)
-  return __ffsll((long long)x) - 1;
+  const uint32_t lo = (uint32_t)x, hi = (uint32_t)(x >> 32);
+  return lo ? __ffs((int)lo) - 1 : 32 + __ffs((int)hi) - 1;
 #else
   return __builtin_ctzll(x);
 #endif
@@ -136,15 +146,18 @@ CW_HD void civil_from_days(int32_t z, int32_t& y, int32_t& m, int32_t& d) {
   m = (int32_t)(mp < 10u ? mp + 3u : mp - 9u);
   y = (int32_t)yoe + era * 400 + (m <= 2);
 }
-CW_HD bool is_leap(int32_t y) { return (y % 4 == 0) && (y % 100 != 0 || y % 400 == 0); }
+CW_HD bool is_leap(int32_t y) {  // y % 100 == 0 <=> y % 25 == 0 given y % 4 == 0; y % 400 == 0 <=> additionally y % 16 == 0
+  return ((y & 3) == 0) && ((y % 25 != 0) || ((y & 15) == 0));
+}
+// days before month m (1..13; 13 = next January) in a non-leap year
+CW_HD int32_t days_before_month(int32_t m) { return (367 * m - 362) / 12 - (m > 2 ? 2 : 0); }
 CW_HD int32_t days_in_month(int32_t y, int32_t m) {
   // 31 for 1,3,5,7,8,10,12; 30 for 4,6,9,11; February by leap rule
-  if (m == 2) return is_leap(y) ? 29 : 28;
-  return 30 + (int32_t)((0x15AAu >> m) & 1u);
+  return (m == 2) ? (is_leap(y) ? 29 : 28) : 30 + (int32_t)((0x15AAu >> m) & 1u);
 }
 CW_HD int32_t weekday_of(int32_t dn) {  // Sunday = 0; 1970-01-01 was a Thursday
-  int32_t w = (dn + 4) % 7;
-  return w < 0 ? w + 7 : w;
+  // 1073741823 = 7 * 153391689: keeps the dividend non-negative for every supported day number (unsigned mod 7)
+  return (int32_t)(((uint32_t)(dn + 4 + 1073741823)) % 7u);
 }
 
 // ---- the walk ------------------------------------------------------------------------------------------------
@@ -415,19 +428,22 @@ CW_HD int64_t walk_next(const Spec& s, Walk& w) {
 }
 
 
-// first matching time of day >= (h, mi, sc), or -1
-CW_HD int32_t next_tod_ge(const Spec& s, int32_t h, int32_t mi, int32_t sc) {
-  if ((s.hour >> h) & 1u) {
-    if ((s.minute >> mi) & 1ULL) {
-      const uint64_t m = s.second >> sc;
-      if (m) return h * 3600 + mi * 60 + sc + ctz64(m);
-    }
-    const uint64_t m = s.minute & ~((2ULL << mi) - 1ULL);
-    if (m) return h * 3600 + ctz64(m) * 60 + ctz64(s.second);
-  }
-  const uint32_t hm = s.hour & ~((2u << h) - 1u);
-  if (hm) return ctz32(hm) * 3600 + ctz64(s.minute) * 60 + ctz64(s.second);
-  return -1;
+// first matching time of day >= sod on the same day, or -1.  Branch-free: the three candidates (same minute, later
+// minute of the same hour, later hour) are all computed and the earliest valid one is selected.
+CW_HD int32_t next_tod_ge(const Spec& s, int32_t sod) {
+  const int32_t h = sod / 3600, rem = sod - h * 3600, mi = rem / 60, sc = rem - mi * 60;
+  const bool hourbit = (s.hour >> h) & 1u;
+  const bool minbit = (s.minute >> mi) & 1ULL;
+  const uint64_t sec_m = s.second >> sc;
+  const uint64_t min_m = (s.minute >> mi) >> 1;
+  const uint32_t hour_m = (s.hour >> h) >> 1;
+  const int32_t c1 = sod + ctz64(sec_m | (1ULL << 62));
+  const int32_t c2 = h * 3600 + (mi + 1 + ctz64(min_m | (1ULL << 62))) * 60 + s.first_s;
+  const int32_t c3 = (h + 1 + ctz32(hour_m | (1u << 30))) * 3600 + s.first_ms;
+  int32_t tod = hour_m ? c3 : -1;
+  tod = (hourbit && min_m) ? c2 : tod;
+  tod = (hourbit && minbit && sec_m) ? c1 : tod;
+  return tod;
 }
 
 // Closed-form Next() from the resident state (t = input + 1s).  Returns true and leaves `w` on the result (or sets
@@ -442,51 +458,69 @@ CW_HD int32_t next_tod_ge(const Spec& s, int32_t h, int32_t mi, int32_t sc) {
 // counted in the zone table (fpre), so "none between here and the fire day" is two loads.  Add-based loops run on
 // t's own day (until the fire, or until the Hour()==0 wrap at the next midnight) and on the fire day from its
 // midnight: both stretches must sit inside one period.  Offsets must be whole minutes (Truncate is absolute).
+//
+// The code is straight-line on purpose (one lane per spec, 32 specs per warp): the only data-dependent control flow
+// is the trip count of the month loop, which visits matching months only.
 CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
   const int32_t sod = w.sod;
-  const int32_t h = sod / 3600, mi = (sod - h * 3600) / 60, sc = sod - h * 3600 - mi * 60;
   const bool zoned = w.zn > 1;
   if (zoned) {
     if (w.off % 60 != 0) return false;
-    if (!w.natural((int64_t)w.dn * 86400 + h * 3600)) return false;  // hour reset Date(Y,M,D,h,0,0)
+    if (!w.natural((int64_t)w.dn * 86400 + (sod / 3600) * 3600)) return false;  // hour reset Date(Y,M,D,h,0,0)
   }
-  const bool today = ((s.month >> w.M) & 1u) && day_matches(s, w.D, w.dn);
-  if (today) {
-    const int32_t tod = next_tod_ge(s, h, mi, sc);
-    if (tod >= 0) {
-      const int64_t r = w.t + (tod - sod);
-      if (r >= w.pe) return false;
-      w.t = r;
-      w.sod = tod;
-      *out = r;
-      return true;
-    }
-    if (w.t + (86400 - sod) >= w.pe) return false;  // the wrap at the next local midnight must happen in this period
+  const bool month_ok = (s.month >> w.M) & 1u;
+  const bool today = month_ok && day_matches(s, w.D, w.dn);
+  const int32_t tod = next_tod_ge(s, sod);
+  if (today && tod >= 0) {
+    const int64_t r = w.t + (tod - sod);
+    if (r >= w.pe) return false;
+    w.t = r;
+    w.sod = tod;
+    *out = r;
+    return true;
   }
-  // ---- calendar search for the next matching day after today ----
+  if (today && w.t + (86400 - sod) >= w.pe) return false;  // the Hour()==0 wrap must happen inside this period
+
+  // ---- calendar search for the next matching day after today, visiting matching months only ----
   const int32_t year_limit = w.Y + 5;
-  int32_t Yc = w.Y, Mc = w.M, Dc = 0;
+  int32_t Yc = w.Y, Mc = w.M;
+  bool leap = is_leap(Yc);
+  int32_t jan1 = w.dn - (w.D - 1) - days_before_month(Mc) - ((leap && Mc > 2) ? 1 : 0);
   int32_t first_dn = w.dn - (w.D - 1);
-  bool found = false;
-  if ((s.month >> Mc) & 1u) {
-    const uint32_t dm = month_daymask(s, Yc, Mc, first_dn) & ~((2u << w.D) - 1u);
-    if (dm) { Dc = ctz32(dm); found = true; }
-  }
-  while (!found) {
+  uint32_t keep = ~((2u << w.D) - 1u);  // current month: days after today
+  bool in_month = month_ok;             // is (Yc, Mc) a month to examine?
+  uint32_t dm = 0;
+  for (;;) {
+    if (in_month) {
+      const int32_t dim = days_before_month(Mc + 1) - days_before_month(Mc) + ((leap && Mc == 2) ? 1 : 0);
+      const uint32_t valid = (uint32_t)((2ULL << dim) - 2ULL);
+      const uint64_t rep = (uint64_t)s.dow * 0x0000000810204081ULL;  // dow pattern repeated every 7 bits
+      const uint32_t dowm = (uint32_t)((rep >> weekday_of(first_dn)) << 1);
+      dm = (s.star ? (s.dom & dowm) : (s.dom | dowm)) & valid & keep;
+      if (dm) break;
+    }
     const uint32_t later = s.month & ~((2u << Mc) - 1u);
-    if (later) { Mc = ctz32(later); } else { ++Yc; Mc = ctz32(s.month); }
-    if (Yc > year_limit) break;
-    first_dn = days_from_civil(Yc, Mc, 1);
-    const uint32_t dm = month_daymask(s, Yc, Mc, first_dn);
-    if (dm) { Dc = ctz32(dm); found = true; }
+    if (later) {
+      Mc = ctz32(later);
+    } else {
+      jan1 += 365 + (leap ? 1 : 0);
+      ++Yc;
+      leap = is_leap(Yc);
+      Mc = ctz32(s.month);
+      if (Yc > year_limit) break;
+    }
+    first_dn = jan1 + days_before_month(Mc) + ((leap && Mc > 2) ? 1 : 0);
+    keep = ~1u;
+    in_month = true;
   }
-  const int32_t found_dn = found ? first_dn + Dc - 1 : days_from_civil(year_limit + 1, 1, 1);
-  const int64_t x_mid = (int64_t)found_dn * 86400;  // local midnight of the fire day (or of the limit's Jan 1)
-  const int32_t tod1 = ctz32(s.hour) * 3600 + ctz64(s.minute) * 60 + ctz64(s.second);
+  const bool found = dm != 0;
+  const int32_t Dc = found ? ctz32(dm) : 1;
+  const int32_t found_dn = found ? first_dn + Dc - 1 : jan1;  // not found: Jan 1 of year_limit + 1 (the WRAP that fails)
+  const int64_t x_mid = (int64_t)found_dn * 86400;            // local midnight of the fire day
   if (!zoned) {
     if (!found) { *out = kZero; return true; }
-    w.t = x_mid + tod1 - w.off;
-    w.dn = found_dn; w.sod = tod1; w.Y = Yc; w.M = Mc; w.D = Dc;
+    w.t = x_mid + s.tod1 - w.off;
+    w.dn = found_dn; w.sod = s.tod1; w.Y = Yc; w.M = Mc; w.D = Dc;
     *out = w.t;
     return true;
   }
@@ -495,11 +529,11 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
   int32_t i_lo = 0;
   if (total_flagged != 0) {
     // earliest Date() target: the 1st of t's month when the month is reset, else today's midnight
-    const int64_t x_lo = (int64_t)(((s.month >> w.M) & 1u) ? w.dn : (w.dn - (w.D - 1))) * 86400;
+    const int64_t x_lo = (int64_t)(month_ok ? w.dn : (w.dn - (w.D - 1))) * 86400;
     w.lookup(x_lo - w.off - 2 * 86400);
     i_lo = w.pidx;
   }
-  int32_t o = w.lookup(x_mid);
+  const int32_t o = w.lookup(x_mid);
   if (o != 0) {
     const int32_t o2 = w.lookup(x_mid - o);
     if (o2 != o) return false;
@@ -513,10 +547,10 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
   }
   if (!found) { *out = kZero; return true; }
   if (o % 60 != 0) return false;
-  const int64_t r = u_mid + tod1;
+  const int64_t r = u_mid + s.tod1;
   if (r >= w.pe) return false;
   w.t = r;
-  w.dn = found_dn; w.sod = tod1; w.Y = Yc; w.M = Mc; w.D = Dc;
+  w.dn = found_dn; w.sod = s.tod1; w.Y = Yc; w.M = Mc; w.D = Dc;
   *out = r;
   return true;
 }
