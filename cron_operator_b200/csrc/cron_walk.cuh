@@ -75,10 +75,12 @@ CW_HD Spec make_spec(uint64_t second, uint64_t minute, uint64_t hour, uint64_t d
   s.dow = (uint32_t)(dow & 0x7Fu);
   s.star = ((dom | dow) >> 63) != 0;
   const bool no_day = s.star ? (s.dom == 0 || s.dow == 0) : (s.dom == 0 && s.dow == 0);
-  s.never = s.second == 0 || s.minute == 0 || s.hour == 0 || s.month == 0 || no_day;
-  s.first_s = ctz64(s.second | (1ULL << 60));
-  s.first_ms = ctz64(s.minute | (1ULL << 60)) * 60 + s.first_s;
-  s.tod1 = ctz32(s.hour | (1u << 24)) * 3600 + s.first_ms;
+  // first set positions with a sentinel bit above the valid range: an empty mask shows up as the sentinel
+  const int32_t fs = ctz64(s.second | (1ULL << 60)), fm = ctz64(s.minute | (1ULL << 60)), fh = ctz32(s.hour | (1u << 24));
+  s.never = (fs == 60) | (fm == 60) | (fh == 24) | (s.month == 0) | no_day;
+  s.first_s = fs;
+  s.first_ms = fm * 60 + fs;
+  s.tod1 = fh * 3600 + s.first_ms;
   return s;
 }
 
@@ -136,21 +138,33 @@ CW_HD int32_t days_from_civil(int32_t y, int32_t m, int32_t d) {  // proleptic G
   return era * 146097 + (int32_t)doe - 719468;
 }
 CW_HD void civil_from_days(int32_t z, int32_t& y, int32_t& m, int32_t& d) {
-  z += 719468;
-  const int32_t era = (z >= 0 ? z : z - 146096) / 146097;
-  const uint32_t doe = (uint32_t)(z - era * 146097);
-  const uint32_t yoe = (doe - doe / 1460u + doe / 36524u - doe / 146096u) / 365u;
-  const uint32_t doy = doe - (365u * yoe + yoe / 4u - yoe / 100u);
-  const uint32_t mp = (5u * doy + 2u) / 153u;
-  d = (int32_t)(doy - (153u * mp + 2u) / 5u + 1u);
-  m = (int32_t)(mp < 10u ? mp + 3u : mp - 9u);
-  y = (int32_t)yoe + era * 400 + (m <= 2);
+  // Neri & Schneider, "Euclidean affine functions and their application to calendar algorithms" (2022), 32-bit
+  // variant on days since 0000-03-01; exact for every day number of the supported range (years 1..9999, checked
+  // exhaustively against the textbook algorithm in tests/test_walk_host.py through the host build).
+  const uint32_t n = (uint32_t)(z + 719468);
+  const uint32_t n1 = 4u * n + 3u;
+  const uint32_t c = n1 / 146097u;
+  const uint32_t nc = (n1 - c * 146097u) / 4u;
+  const uint32_t n2 = 4u * nc + 3u;
+  const uint64_t p2 = 2939745ULL * n2;
+  const uint32_t zc = (uint32_t)(p2 >> 32);
+  const uint32_t ny = (uint32_t)p2 / 2939745u / 4u;
+  const uint32_t n3 = 2141u * ny + 197913u;
+  const uint32_t mm = n3 >> 16;
+  const uint32_t dd = (n3 & 0xffffu) / 2141u;
+  const bool j = ny >= 306u;
+  y = (int32_t)(100u * c + zc) + (j ? 1 : 0);
+  m = (int32_t)(j ? mm - 12u : mm);
+  d = (int32_t)dd + 1;
 }
 CW_HD bool is_leap(int32_t y) {  // y % 100 == 0 <=> y % 25 == 0 given y % 4 == 0; y % 400 == 0 <=> additionally y % 16 == 0
   return ((y & 3) == 0) && ((y % 25 != 0) || ((y & 15) == 0));
 }
 // days before month m (1..13; 13 = next January) in a non-leap year
-CW_HD int32_t days_before_month(int32_t m) { return (367 * m - 362) / 12 - (m > 2 ? 2 : 0); }
+CW_HD int32_t days_before_month(int32_t m) {
+  // 30*(m-1) plus a 3-bit correction per month packed into one constant (no division)
+  return 30 * m - 31 + (int32_t)((0x35B23489088ULL >> (3 * m)) & 7ULL);
+}
 CW_HD int32_t days_in_month(int32_t y, int32_t m) {
   // 31 for 1,3,5,7,8,10,12; 30 for 4,6,9,11; February by leap rule
   return (m == 2) ? (is_leap(y) ? 29 : 28) : 30 + (int32_t)((0x15AAu >> m) & 1u);
@@ -469,8 +483,19 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
     if (!w.natural((int64_t)w.dn * 86400 + (sod / 3600) * 3600)) return false;  // hour reset Date(Y,M,D,h,0,0)
   }
   const bool month_ok = (s.month >> w.M) & 1u;
-  const bool today = month_ok && day_matches(s, w.D, w.dn);
   const int32_t tod = next_tod_ge(s, sod);
+  // day mask of the current month, evaluated by every lane before any branch
+  bool leap = is_leap(w.Y);
+  int32_t first_dn = w.dn - (w.D - 1);
+  const uint64_t rep = (uint64_t)s.dow * 0x0000000810204081ULL;  // dow pattern repeated every 7 bits
+  uint32_t dm;
+  {
+    const int32_t dim = (w.M == 2) ? (leap ? 29 : 28) : 30 + (int32_t)((0x15AAu >> w.M) & 1u);
+    const uint32_t valid = (uint32_t)((2ULL << dim) - 2ULL);
+    const uint32_t dowm = (uint32_t)((rep >> weekday_of(first_dn)) << 1);
+    dm = month_ok ? ((s.star ? (s.dom & dowm) : (s.dom | dowm)) & valid) : 0u;
+  }
+  const bool today = (dm >> w.D) & 1u;  // == month matches && dayMatches(t)
   if (today && tod >= 0) {
     const int64_t r = w.t + (tod - sod);
     if (r >= w.pe) return false;
@@ -484,21 +509,9 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
   // ---- calendar search for the next matching day after today, visiting matching months only ----
   const int32_t year_limit = w.Y + 5;
   int32_t Yc = w.Y, Mc = w.M;
-  bool leap = is_leap(Yc);
-  int32_t jan1 = w.dn - (w.D - 1) - days_before_month(Mc) - ((leap && Mc > 2) ? 1 : 0);
-  int32_t first_dn = w.dn - (w.D - 1);
-  uint32_t keep = ~((2u << w.D) - 1u);  // current month: days after today
-  bool in_month = month_ok;             // is (Yc, Mc) a month to examine?
-  uint32_t dm = 0;
-  for (;;) {
-    if (in_month) {
-      const int32_t dim = days_before_month(Mc + 1) - days_before_month(Mc) + ((leap && Mc == 2) ? 1 : 0);
-      const uint32_t valid = (uint32_t)((2ULL << dim) - 2ULL);
-      const uint64_t rep = (uint64_t)s.dow * 0x0000000810204081ULL;  // dow pattern repeated every 7 bits
-      const uint32_t dowm = (uint32_t)((rep >> weekday_of(first_dn)) << 1);
-      dm = (s.star ? (s.dom & dowm) : (s.dom | dowm)) & valid & keep;
-      if (dm) break;
-    }
+  int32_t jan1 = first_dn - days_before_month(Mc) - ((leap && Mc > 2) ? 1 : 0);
+  dm &= ~((2u << w.D) - 1u);  // current month: days after today
+  while (dm == 0) {
     const uint32_t later = s.month & ~((2u << Mc) - 1u);
     if (later) {
       Mc = ctz32(later);
@@ -510,8 +523,10 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
       if (Yc > year_limit) break;
     }
     first_dn = jan1 + days_before_month(Mc) + ((leap && Mc > 2) ? 1 : 0);
-    keep = ~1u;
-    in_month = true;
+    const int32_t dim = (Mc == 2) ? (leap ? 29 : 28) : 30 + (int32_t)((0x15AAu >> Mc) & 1u);
+    const uint32_t valid = (uint32_t)((2ULL << dim) - 2ULL);
+    const uint32_t dowm = (uint32_t)((rep >> weekday_of(first_dn)) << 1);
+    dm = (s.star ? (s.dom & dowm) : (s.dom | dowm)) & valid;
   }
   const bool found = dm != 0;
   const int32_t Dc = found ? ctz32(dm) : 1;

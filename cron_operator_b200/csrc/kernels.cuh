@@ -47,12 +47,12 @@ __device__ __forceinline__ bool bind_checked(Walk& w, const ZoneTable& zt, int32
 //   KT = 0 (any other k): transposed staging [j][row] and a division per element on the way out.
 // Algorithmic bytes: 48 (masks) + 8 (from) [+ 4 zone] in, 8k out per spec.
 // -------------------------------------------------------------------------------------------------------------
-constexpr int kNextThreads = 128;
+constexpr int kNextThreads = 64;
 constexpr int kNextWarpTile = 64;
 constexpr int kNextTile = kNextWarpTile * (kNextThreads / 32);
 
 template <int KT, bool kVec>
-__global__ void __launch_bounds__(kNextThreads)
+__global__ void __launch_bounds__(kNextThreads, 16)
 next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* __restrict__ from, size_t n, int k_rt,
               int64_t* __restrict__ out, ZoneTable zt, int* __restrict__ err) {
   extern __shared__ __align__(16) int64_t stage_all[];  // [warps][64 * k], unused when KT == 1

@@ -156,3 +156,31 @@ def test_next_historic_and_far_future_zones():
         got = shim.next_n(masks, frm, k=3, zone_id=zid)
         want = po.batch_next_n(masks, frm, k=3, zone_id=zid, zone_names=NAMES)
         assert np.array_equal(got, want), name
+
+
+def test_calendar_primitives_exhaustive():
+    """the kernels' civil-from-days (Neri-Schneider) and days-before-month against python's calendar: every day of
+    years 1..9999 through the host build (next fire of '0 0 * * *' from 23:59:59 UTC is the next midnight, and
+    '0 0 1 * *' exercises month lengths / leap years)"""
+    import datetime as dt
+    first = dt.date(1, 1, 2).toordinal() - dt.date(1970, 1, 1).toordinal()
+    last = dt.date(9993, 12, 31).toordinal() - dt.date(1970, 1, 1).toordinal()
+    days = np.arange(first, last, dtype=np.int64)
+    frm = days * 86400 - 1                                   # 23:59:59 of the previous day
+    daily = _masks_of(["0 0 * * *"])
+    got = shim.next_n(np.ascontiguousarray(np.repeat(daily, len(days), axis=1)), frm, 1)[:, 0]
+    assert np.array_equal(got, days * 86400)
+    # monthly: the next fire must be the first of the next month per python's calendar
+    monthly = _masks_of(["0 0 1 * *"])
+    got = shim.next_n(np.ascontiguousarray(np.repeat(monthly, len(days), axis=1)), days * 86400, 1)[:, 0]
+    ords = days + dt.date(1970, 1, 1).toordinal()
+    want = np.empty(len(days), dtype=np.int64)
+    cache = {}
+    for i, o in enumerate(ords[::1]):
+        d = dt.date.fromordinal(int(o))
+        key = (d.year, d.month)
+        if key not in cache:
+            ny, nm = (d.year + 1, 1) if d.month == 12 else (d.year, d.month + 1)
+            cache[key] = (dt.date(ny, nm, 1).toordinal() - dt.date(1970, 1, 1).toordinal()) * 86400
+        want[i] = cache[key]
+    assert np.array_equal(got, want)
