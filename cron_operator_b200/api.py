@@ -56,7 +56,7 @@ def lib():
     global _LIB
     if _LIB is not None:
         return _LIB
-    path = _build.build()
+    path = os.environ.get("B200CRON_LIB") or _build.build()  # B200CRON_LIB: tuning builds (see profiles/)
     L = C.CDLL(path)
     vp, sz, i32, i64 = C.c_void_p, C.c_size_t, C.c_int, C.c_int64
     for f in (L.b200cron_parse_standard, L.b200cron_parse_with_seconds):

@@ -570,8 +570,11 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
   return true;
 }
 
-// Next(t): t.Add(1s) then the walk.  `resident` = w already holds the fields of `t` (chained NextN calls).
-CW_HD int64_t next_from(const Spec& s, Walk& w, int64_t t, bool resident) {
+// Next(t) in two halves so that kernels can run the straight-line half for several specs in lock step and share one
+// copy of the step emulation: next_try() = t.Add(1s), field decomposition and the closed form; it returns false when
+// only walk_next() can decide (then call next_slow()).  `resident` = w already holds the fields of `t`.
+CW_HD bool next_try(const Spec& s, Walk& w, int64_t t, bool resident, int64_t* out) {
+  if (s.never) { *out = kZero; return true; }
   const int64_t t1 = t + 1;
   if (resident && t1 < w.pe && w.sod + 1 < 86400) {
     w.t = t1;
@@ -579,11 +582,16 @@ CW_HD int64_t next_from(const Spec& s, Walk& w, int64_t t, bool resident) {
   } else {
     w.load(t1);
   }
-  if (s.never) return kZero;
-  int64_t r;
-  if (fast_next(s, w, &r)) return r;
+  return fast_next(s, w, out);
+}
+CW_HD int64_t next_slow(const Spec& s, Walk& w) {
   w.lookup(w.t);  // fast_next may have moved the period cache; the step emulation wants it on t
   return walk_next(s, w);
+}
+CW_HD int64_t next_from(const Spec& s, Walk& w, int64_t t, bool resident) {
+  int64_t r;
+  if (next_try(s, w, t, resident, &r)) return r;
+  return next_slow(s, w);
 }
 
 }  // namespace cronwalk

@@ -27,6 +27,7 @@ struct MaskPlanes {
 };
 
 __device__ __forceinline__ bool bind_checked(Walk& w, const ZoneTable& zt, int32_t zone, int64_t t, int* err) {
+  w.bind_utc();
   if (t < kMinTime || t > kMaxTime) { atomicOr(err, kErrRange); return false; }
   if (zone == 0) { w.bind_utc(); return true; }
   if (zone < 0 || zone >= zt.nzones) { atomicOr(err, kErrZone); return false; }
@@ -52,7 +53,7 @@ constexpr int kNextWarpTile = 64;
 constexpr int kNextTile = kNextWarpTile * (kNextThreads / 32);
 
 template <int KT, bool kVec>
-__global__ void __launch_bounds__(kNextThreads, 16)
+__global__ void __launch_bounds__(kNextThreads, 10)
 next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* __restrict__ from, size_t n, int k_rt,
               int64_t* __restrict__ out, ZoneTable zt, int* __restrict__ err) {
   extern __shared__ __align__(16) int64_t stage_all[];  // [warps][64 * k], unused when KT == 1
@@ -91,36 +92,48 @@ next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* 
     }
   }
 
-  int64_t ra = kZero, rb = kZero;
+  // The lane's two specs run in lock step (unrolled): two independent dependency chains per lane keep the issue
+  // slots busy with fewer resident warps.
+  Spec sp[2];
+  Walk w[2];
+  int64_t t[2];
+  bool ok[2];
+#pragma unroll
+  for (int e = 0; e < 2; ++e) {
+    sp[e] = cronwalk::make_spec(mk[0][e], mk[1][e], mk[2][e], mk[3][e], mk[4][e], mk[5][e]);
+    t[e] = fr[e];
+    ok[e] = (i0 + e < n) && bind_checked(w[e], zt, zz[e], t[e], err);
+  }
+  const int kk = KT == 1 ? 1 : k;
 #pragma unroll 1
-  for (int e = 0; e < 2; ++e) {  // one copy of the walk in the instruction stream; operands picked with selects
-    if (i0 + e >= n) break;
-    const Spec s = e ? cronwalk::make_spec(mk[0][1], mk[1][1], mk[2][1], mk[3][1], mk[4][1], mk[5][1])
-                     : cronwalk::make_spec(mk[0][0], mk[1][0], mk[2][0], mk[3][0], mk[4][0], mk[5][0]);
-    Walk w;
-    int64_t t = e ? fr[1] : fr[0];
-    bool ok = bind_checked(w, zt, e ? zz[1] : zz[0], t, err);
-    if (KT == 1) {
-      const int64_t r = ok ? cronwalk::next_from(s, w, t, false) : kZero;
-      if (e) rb = r; else ra = r;
-    } else {
-      bool resident = false;
-      const int row = 2 * lane + e;
+  for (int j = 0; j < kk; ++j) {
+    bool need[2];
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      need[e] = false;
+      if (ok[e] && t[e] != kZero) need[e] = !cronwalk::next_try(sp[e], w[e], t[e], j > 0, &t[e]);
+      else t[e] = kZero;
+    }
+    if (need[0] | need[1]) {  // rare: a zone transition (or an unnatural Date() target) is in the way
 #pragma unroll 1
-      for (int j = 0; j < k; ++j) {
-        if (ok && t != kZero) {
-          t = cronwalk::next_from(s, w, t, resident);
-          resident = true;
-          // chained calls keep walking: re-check the zoned horizon (UTC never trips it)
-          if (t != kZero && w.zn > 1 && t >= zt.horizon - kSixYears) { atomicOr(err, kErrRange); ok = false; t = kZero; }
-        } else {
-          t = kZero;
-        }
-        if (KT > 1) stage[row * KT + ((j + lane) & (KT - 1))] = t;
-        else stage[j * kNextWarpTile + row] = t;
+      for (int e = 0; e < 2; ++e) {
+        if (!(e ? need[1] : need[0])) continue;
+        const Spec ss = e ? sp[1] : sp[0];
+        Walk ww = e ? w[1] : w[0];
+        const int64_t r = cronwalk::next_slow(ss, ww);
+        if (e) { w[1] = ww; t[1] = r; } else { w[0] = ww; t[0] = r; }
       }
     }
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      // chained calls keep walking: re-check the zoned horizon (UTC never trips it)
+      if (KT != 1 && t[e] != kZero && w[e].zn > 1 && t[e] >= zt.horizon - kSixYears) { atomicOr(err, kErrRange); ok[e] = false; t[e] = kZero; }
+      const int row = 2 * lane + e;
+      if (KT > 1) stage[row * KT + ((j + lane) & (KT - 1))] = t[e];
+      else if (KT == 0) stage[j * kNextWarpTile + row] = t[e];
+    }
   }
+  const int64_t ra = t[0], rb = t[1];
 
   if (KT == 1) {
     if (kVec && full) {
