@@ -201,7 +201,7 @@ def main():
 
     import torch
     import torch.distributed as dist
-    from cron_operator_b200 import api
+    from cron_operator_b200 import api, shard
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -274,10 +274,7 @@ def main():
     clocks = sampler.stop() if rank == 0 else None
     assert np.array_equal(h_out.array, d_out.cpu().numpy()), "host-pointer and device-pointer paths disagree"
 
-    if world > 1:
-        tt = torch.tensor([dev_s, e2e_s], dtype=torch.float64, device="cuda")
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        dev_s, e2e_s = tt.tolist()
+    dev_s, e2e_s = shard.max_over_ranks([dev_s, e2e_s], device="cuda")  # max over ranks (identity at N=1)
 
     if rank == 0:
         value = world * N_SPECS * args.steps / dev_s

@@ -84,6 +84,12 @@ def lib():
     L.b200cron_unmet_since.argtypes = [vp, vp, vp, vp, i64, C.c_int32, vp, vp, vp, vp, sz, vp, vp, vp, vp, vp]
     L.b200cron_unmet_since_dev.restype = i32
     L.b200cron_unmet_since_dev.argtypes = [vp, i32, vp, vp, vp, vp, i64, C.c_int32, vp, vp, vp, vp, sz, vp, vp, vp, vp, vp]
+    L.b200cron_unmet_list.restype = i32
+    L.b200cron_unmet_list.argtypes = [vp, vp, vp, vp, vp, vp, sz, C.c_uint32, vp, vp, sz]
+    L.b200cron_unmet_list_offsets_dev.restype = i32
+    L.b200cron_unmet_list_offsets_dev.argtypes = [vp, i32, vp, vp, vp, sz, C.c_uint32, vp]
+    L.b200cron_unmet_list_emit_dev.restype = i32
+    L.b200cron_unmet_list_emit_dev.argtypes = [vp, i32, vp, vp, vp, vp, sz, vp, vp]
     L.b200cron_history_prune.restype = i32
     L.b200cron_history_prune.argtypes = [vp, vp, vp, vp, sz, vp, vp]
     L.b200cron_history_prune_dev.restype = i32
@@ -256,6 +262,30 @@ class Context:
                                                out["missed"].ctypes.data, out["status"].ctypes.data,
                                                out["decision"].ctypes.data))
         return out
+
+    def unmet_list(self, masks: np.ndarray, earliest, missed, decision, cap: int = 100, zone_id=None):
+        """the first min(missed, cap) missed fire times per Cron: (list_off[n+1], list) -- cap 100 mirrors the
+        TooManyMissedTimes threshold (cron_controller.go:431)"""
+        planes, n = _planes(masks)
+        earliest = np.ascontiguousarray(earliest, dtype=np.int64)
+        missed = np.ascontiguousarray(missed, dtype=np.uint32)
+        decision = np.ascontiguousarray(decision, dtype=np.uint8)
+        zid = None if zone_id is None else np.ascontiguousarray(zone_id, dtype=np.int32)
+        off = np.empty(n + 1, np.uint64)
+        total = int(np.minimum(missed, cap)[decision >= DEC_REQUEUE_ONLY].sum())
+        lst = np.empty(total, np.int64)
+        self._check(lib().b200cron_unmet_list(self._h, planes, _ptr(zid), earliest.ctypes.data, missed.ctypes.data,
+                                              decision.ctypes.data, n, cap, off.ctypes.data, lst.ctypes.data, total))
+        return off, lst
+
+    def unmet_list_offsets_dev(self, missed, decision, list_off, cap: int = 100, dev_index: int = 0, stream: int = 0):
+        self._check(lib().b200cron_unmet_list_offsets_dev(self._h, dev_index, stream or None, _ptr(missed),
+                                                          _ptr(decision), missed.numel(), cap, _ptr(list_off)))
+
+    def unmet_list_emit_dev(self, masks, earliest, list_off, out_list, zone_id=None, dev_index: int = 0, stream: int = 0):
+        planes, n = _planes(masks)
+        self._check(lib().b200cron_unmet_list_emit_dev(self._h, dev_index, stream or None, planes, _ptr(zone_id),
+                                                       _ptr(earliest), n, _ptr(list_off), _ptr(out_list)))
 
     def history_prune(self, seg_off, key, limit=None):
         seg_off = np.ascontiguousarray(seg_off, dtype=np.uint64)

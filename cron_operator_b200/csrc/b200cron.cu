@@ -44,6 +44,8 @@ struct Device {
   int* d_err = nullptr;
   int* h_err = nullptr;  // pinned mirror
   Slot slots[kSlots];
+  uint64_t* d_scratch = nullptr;  // per-tile sums of the unmet-list prefix sum
+  size_t scratch_cap = 0;         // entries
   ZoneTable zt{};
 };
 
@@ -270,6 +272,7 @@ extern "C" void b200cron_ctx_destroy(b200cron_ctx* ctx) {
     if (d.d_fpre) cudaFree(d.d_fpre);
     if (d.d_zstart) cudaFree(d.d_zstart);
     if (d.d_err) cudaFree(d.d_err);
+    if (d.d_scratch) cudaFree(d.d_scratch);
     if (d.h_err) cudaFreeHost(d.h_err);
   }
   delete ctx;
@@ -485,6 +488,128 @@ extern "C" int b200cron_unmet_since(b200cron_ctx* ctx, const uint64_t* const mas
     CU(ctx, cudaStreamSynchronize(d.stream));
   }
   return check_err_flags(ctx);
+}
+
+
+// =================================================================================================================
+// unmet list
+// =================================================================================================================
+namespace {
+
+int launch_list_offsets(b200cron_ctx* ctx, Device& d, cudaStream_t st, const uint32_t* missed, const uint8_t* decision,
+                        size_t n, uint32_t cap, uint64_t* list_off, uint64_t* tile_sums) {
+  const size_t ntiles = (n + kScanTile - 1) / kScanTile;
+  ctx->launches.fetch_add(3, std::memory_order_relaxed);
+  list_tile_sums_kernel<<<(unsigned)ntiles, kScanThreads, 0, st>>>(missed, decision, n, cap, tile_sums);
+  list_scan_sums_kernel<<<1, kScanThreads, 0, st>>>(tile_sums, ntiles);
+  list_offsets_kernel<<<(unsigned)ntiles, kScanThreads, 0, st>>>(missed, decision, n, cap, tile_sums, list_off);
+  CU(ctx, cudaGetLastError());
+  (void)d;
+  return 0;
+}
+
+int ensure_scratch(b200cron_ctx* ctx, Device& d, size_t entries) {
+  if (entries <= d.scratch_cap) return 0;
+  if (d.d_scratch) CU(ctx, cudaFree(d.d_scratch));
+  d.d_scratch = nullptr;
+  d.scratch_cap = 0;
+  CU(ctx, cudaMalloc(&d.d_scratch, entries * sizeof(uint64_t)));
+  d.scratch_cap = entries;
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int b200cron_unmet_list_offsets_dev(b200cron_ctx* ctx, int dev_index, void* stream, const uint32_t* missed,
+                                               const uint8_t* decision, size_t n, uint32_t cap, uint64_t* list_off) {
+  Device* d = device_at(ctx, dev_index);
+  if (!d) return B200CRON_EINVAL;
+  if (!missed || !decision || !list_off) return fail(ctx, B200CRON_EINVAL, "unmet_list_offsets: NULL argument");
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  CU(ctx, cudaSetDevice(d->id));
+  cudaStream_t st = stream ? (cudaStream_t)stream : d->stream;
+  if (n == 0) {
+    CU(ctx, cudaMemsetAsync(list_off, 0, sizeof(uint64_t), st));
+    return B200CRON_OK;
+  }
+  const size_t ntiles = (n + kScanTile - 1) / kScanTile;
+  int rc = ensure_scratch(ctx, *d, ntiles + 1);
+  if (rc) return rc;
+  return launch_list_offsets(ctx, *d, st, missed, decision, n, cap, list_off, d->d_scratch);
+}
+
+extern "C" int b200cron_unmet_list_emit_dev(b200cron_ctx* ctx, int dev_index, void* stream,
+                                            const uint64_t* const masks[6], const int32_t* zone_id,
+                                            const int64_t* earliest, size_t n, const uint64_t* list_off,
+                                            int64_t* list) {
+  Device* d = device_at(ctx, dev_index);
+  if (!d) return B200CRON_EINVAL;
+  if (!masks || !earliest || !list_off) return fail(ctx, B200CRON_EINVAL, "unmet_list_emit: NULL argument");
+  if (n == 0) return B200CRON_OK;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  CU(ctx, cudaSetDevice(d->id));
+  MaskPlanes m;
+  for (int p = 0; p < 6; ++p) m.p[p] = masks[p];
+  ctx->launches.fetch_add(1, std::memory_order_relaxed);
+  unmet_list_emit_kernel<<<(unsigned)((n + kUnmetThreads - 1) / kUnmetThreads), kUnmetThreads, 0,
+                           stream ? (cudaStream_t)stream : d->stream>>>(m, zone_id, earliest, n, list_off, list, d->zt);
+  CU(ctx, cudaGetLastError());
+  return B200CRON_OK;
+}
+
+extern "C" int b200cron_unmet_list(b200cron_ctx* ctx, const uint64_t* const masks[6], const int32_t* zone_id,
+                                   const int64_t* earliest, const uint32_t* missed, const uint8_t* decision, size_t n,
+                                   uint32_t cap, uint64_t* list_off, int64_t* list, size_t list_cap) {
+  if (!ctx) return B200CRON_EINVAL;
+  if (!masks || !earliest || !missed || !decision || !list_off)
+    return fail(ctx, B200CRON_EINVAL, "unmet_list: NULL required argument");
+  if (n == 0) { list_off[0] = 0; return B200CRON_OK; }
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  Device& d = ctx->devs[0];
+  CU(ctx, cudaSetDevice(d.id));
+  Slot& s = d.slots[0];
+  const size_t stride = align_up(n + 1, 64);
+  const size_t ntiles = (n + kScanTile - 1) / kScanTile;
+  // staging: 6 planes | earliest | list_off (8 B) | zone | missed (4 B) | decision (1 B)
+  int rc = ensure_slot(ctx, s, stride * (8 * 8 + 2 * 4 + 1) + 1024);
+  if (rc) return rc;
+  rc = ensure_scratch(ctx, d, ntiles + 1);
+  if (rc) return rc;
+  uint64_t* d_masks = reinterpret_cast<uint64_t*>(s.buf);
+  int64_t* d_earliest = reinterpret_cast<int64_t*>(d_masks + 6 * stride);
+  uint64_t* d_off = reinterpret_cast<uint64_t*>(d_earliest + stride);
+  int32_t* d_zone = reinterpret_cast<int32_t*>(d_off + stride);
+  uint32_t* d_missed = reinterpret_cast<uint32_t*>(d_zone + stride);
+  uint8_t* d_decision = reinterpret_cast<uint8_t*>(d_missed + stride);
+  MaskPlanes m;
+  for (int p = 0; p < 6; ++p) {
+    m.p[p] = d_masks + p * stride;
+    CU(ctx, cudaMemcpyAsync(d_masks + p * stride, masks[p], n * 8, cudaMemcpyHostToDevice, s.stream));
+  }
+  CU(ctx, cudaMemcpyAsync(d_earliest, earliest, n * 8, cudaMemcpyHostToDevice, s.stream));
+  if (zone_id) CU(ctx, cudaMemcpyAsync(d_zone, zone_id, n * 4, cudaMemcpyHostToDevice, s.stream));
+  CU(ctx, cudaMemcpyAsync(d_missed, missed, n * 4, cudaMemcpyHostToDevice, s.stream));
+  CU(ctx, cudaMemcpyAsync(d_decision, decision, n, cudaMemcpyHostToDevice, s.stream));
+  rc = launch_list_offsets(ctx, d, s.stream, d_missed, d_decision, n, cap, d_off, d.d_scratch);
+  if (rc) return rc;
+  CU(ctx, cudaMemcpyAsync(list_off, d_off, (n + 1) * 8, cudaMemcpyDeviceToHost, s.stream));
+  CU(ctx, cudaStreamSynchronize(s.stream));
+  const uint64_t total = list_off[n];
+  if (total > list_cap || (total && !list))
+    return fail(ctx, B200CRON_ENOMEM, "unmet_list: list needs %llu entries, capacity is %llu",
+                (unsigned long long)total, (unsigned long long)list_cap);
+  if (total == 0) return B200CRON_OK;
+  Slot& s1 = d.slots[1];
+  rc = ensure_slot(ctx, s1, total * 8 + 1024);
+  if (rc) return rc;
+  int64_t* d_list = reinterpret_cast<int64_t*>(s1.buf);
+  ctx->launches.fetch_add(1, std::memory_order_relaxed);
+  unmet_list_emit_kernel<<<(unsigned)((n + kUnmetThreads - 1) / kUnmetThreads), kUnmetThreads, 0, s.stream>>>(
+      m, zone_id ? d_zone : nullptr, d_earliest, n, d_off, d_list, d.zt);
+  CU(ctx, cudaGetLastError());
+  CU(ctx, cudaMemcpyAsync(list, d_list, total * 8, cudaMemcpyDeviceToHost, s.stream));
+  CU(ctx, cudaStreamSynchronize(s.stream));
+  return B200CRON_OK;
 }
 
 // =================================================================================================================

@@ -298,4 +298,131 @@ history_prune_kernel(const uint64_t* __restrict__ seg_off, const int64_t* __rest
   }
 }
 
+// -------------------------------------------------------------------------------------------------------------
+// unmet list: the first min(missed, cap) missed fire times of every Cron, packed back to back
+//                                   (the enumeration of cron_controller.go:409-430, which upstream only counts)
+//
+// list_off = exclusive prefix sum of the per-Cron counts (three small kernels: per-tile sums into a scratch array,
+// a single-CTA scan of the tile sums, per-tile offsets = warp-shuffle scan + tile base); unmet_list_emit_kernel then
+// re-walks each chain and writes its fire times at list + list_off[i].  Gated / unschedulable Crons contribute 0.
+// Scratch: one uint64 per tile of kScanTile Crons.
+// -------------------------------------------------------------------------------------------------------------
+constexpr int kScanThreads = 256;
+constexpr int kScanItems = 4;
+constexpr int kScanTile = kScanThreads * kScanItems;
+
+__device__ __forceinline__ uint32_t list_count(uint32_t missed, uint8_t decision, uint32_t cap) {
+  const bool listed = decision >= cronwalk::kDecRequeueOnly;  // REQUEUE_ONLY, SKIP_FORBID, REPLACE_CREATE, CREATE
+  return listed ? (missed < cap ? missed : cap) : 0u;
+}
+
+__device__ __forceinline__ uint32_t warp_inclusive_scan(uint32_t v) {
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t o = __shfl_up_sync(0xffffffffu, v, d);
+    if ((threadIdx.x & 31) >= d) v += o;
+  }
+  return v;
+}
+
+// block-wide exclusive scan of one value per thread; returns the thread's exclusive prefix, *total = block sum
+__device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* total) {
+  __shared__ uint32_t warp_sums[kScanThreads / 32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t inc = warp_inclusive_scan(v);
+  if (lane == 31) warp_sums[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    const uint32_t ws = lane < kScanThreads / 32 ? warp_sums[lane] : 0u;
+    const uint32_t wi = warp_inclusive_scan(ws);
+    if (lane < kScanThreads / 32) warp_sums[lane] = wi - ws;  // exclusive warp bases
+    if (lane == kScanThreads / 32 - 1) *total = wi;
+  }
+  __syncthreads();
+  const uint32_t base = warp_sums[warp];
+  __syncthreads();
+  return base + inc - v;
+}
+
+__global__ void __launch_bounds__(kScanThreads)
+list_tile_sums_kernel(const uint32_t* __restrict__ missed, const uint8_t* __restrict__ decision, size_t n,
+                      uint32_t cap, uint64_t* __restrict__ tile_sums) {
+  __shared__ uint32_t total;
+  const size_t base = (size_t)blockIdx.x * kScanTile + (size_t)threadIdx.x * kScanItems;
+  uint32_t v = 0;
+#pragma unroll
+  for (int q = 0; q < kScanItems; ++q)
+    if (base + q < n) v += list_count(__ldg(missed + base + q), __ldg(decision + base + q), cap);
+  block_exclusive_scan(v, &total);
+  if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
+}
+
+// single CTA: in-place exclusive scan of the tile sums; tile_sums[ntiles] receives the grand total
+__global__ void __launch_bounds__(kScanThreads)
+list_scan_sums_kernel(uint64_t* __restrict__ tile_sums, size_t ntiles) {
+  __shared__ uint64_t carry;
+  __shared__ uint64_t part[kScanThreads];
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (size_t c = 0; c < ntiles; c += kScanThreads) {
+    const size_t i = c + threadIdx.x;
+    const uint64_t v = i < ntiles ? tile_sums[i] : 0;
+    part[threadIdx.x] = v;
+    __syncthreads();
+    for (int d = 1; d < kScanThreads; d <<= 1) {  // Hillis-Steele over one chunk
+      const uint64_t o = threadIdx.x >= d ? part[threadIdx.x - d] : 0;
+      __syncthreads();
+      part[threadIdx.x] += o;
+      __syncthreads();
+    }
+    if (i < ntiles) tile_sums[i] = carry + part[threadIdx.x] - v;
+    __syncthreads();
+    if (threadIdx.x == kScanThreads - 1) carry += part[kScanThreads - 1];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) tile_sums[ntiles] = carry;
+}
+
+__global__ void __launch_bounds__(kScanThreads)
+list_offsets_kernel(const uint32_t* __restrict__ missed, const uint8_t* __restrict__ decision, size_t n, uint32_t cap,
+                    const uint64_t* __restrict__ tile_sums, uint64_t* __restrict__ list_off) {
+  __shared__ uint32_t total;
+  const size_t base = (size_t)blockIdx.x * kScanTile + (size_t)threadIdx.x * kScanItems;
+  uint32_t c[kScanItems];
+  uint32_t v = 0;
+#pragma unroll
+  for (int q = 0; q < kScanItems; ++q) {
+    c[q] = (base + q < n) ? list_count(__ldg(missed + base + q), __ldg(decision + base + q), cap) : 0u;
+    v += c[q];
+  }
+  uint64_t run = tile_sums[blockIdx.x] + block_exclusive_scan(v, &total);
+#pragma unroll
+  for (int q = 0; q < kScanItems; ++q) {
+    if (base + q < n) list_off[base + q] = run;
+    run += c[q];
+  }
+  if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) list_off[n] = tile_sums[gridDim.x];
+}
+
+__global__ void __launch_bounds__(kUnmetThreads)
+unmet_list_emit_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* __restrict__ earliest,
+                       size_t n, const uint64_t* __restrict__ list_off, int64_t* __restrict__ list, ZoneTable zt) {
+  const size_t i = (size_t)blockIdx.x * kUnmetThreads + threadIdx.x;
+  if (i >= n) return;
+  const uint64_t a = __ldg(list_off + i), b = __ldg(list_off + i + 1);
+  if (b == a) return;
+  const Spec s = cronwalk::make_spec(__ldg(m.p[0] + i), __ldg(m.p[1] + i), __ldg(m.p[2] + i), __ldg(m.p[3] + i),
+                                     __ldg(m.p[4] + i), __ldg(m.p[5] + i));
+  const int32_t zone = zone_id ? __ldg(zone_id + i) : 0;
+  Walk w;
+  if (zone == 0) w.bind_utc(); else w.bind_zone(zt, zone);  // ids and ranges were validated by unmet_kernel
+  int64_t t = __ldg(earliest + i);
+  bool resident = false;
+  for (uint64_t j = a; j < b; ++j) {
+    t = cronwalk::next_from(s, w, t, resident);
+    resident = true;
+    list[j] = t;
+  }
+}
+
 }  // namespace b200cron

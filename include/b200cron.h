@@ -142,6 +142,27 @@ int b200cron_unmet_since_dev(b200cron_ctx* ctx, int dev_index, void* stream, con
                              const int64_t* deadline, size_t n, int64_t* last, int64_t* next, uint32_t* missed,
                              uint8_t* status, uint8_t* decision);
 
+/* Optional enumeration of the missed runs themselves.  The reference only counts them (cron_controller.go:409-430,
+ * keeping the last one); callers that want to start every missed run need the times.  Given the `missed` and
+ * `decision` arrays a previous b200cron_unmet_since call produced for the same Crons, writes
+ *   list_off[i] (n+1 entries) = exclusive prefix sum of min(missed[i], cap) over Crons whose decision is
+ *                                REQUEUE_ONLY / SKIP_FORBID / REPLACE_CREATE / CREATE (0 for gated or failed ones), and
+ *   list[list_off[i] .. list_off[i+1]) = that Cron's first min(missed, cap) missed fire times in order.
+ * list_cap is the capacity of `list` in entries; when it is too small the call returns B200CRON_ENOMEM after
+ * filling list_off (list_off[n] is the capacity needed).  The host-pointer variant runs on the context's first
+ * device. */
+int b200cron_unmet_list(b200cron_ctx* ctx, const uint64_t* const masks[6], const int32_t* zone_id,
+                        const int64_t* earliest, const uint32_t* missed, const uint8_t* decision, size_t n,
+                        uint32_t cap, uint64_t* list_off, int64_t* list, size_t list_cap);
+/* Device-pointer variant in two steps so that the caller can size `list` in between: _offsets_dev fills list_off
+ * (the context's scratch buffer holds the per-tile sums; it grows with cudaMalloc on first use or when n grows),
+ * the caller reads list_off[n] after syncing the stream, then _emit_dev writes the fire times. */
+int b200cron_unmet_list_offsets_dev(b200cron_ctx* ctx, int dev_index, void* stream, const uint32_t* missed,
+                                    const uint8_t* decision, size_t n, uint32_t cap, uint64_t* list_off);
+int b200cron_unmet_list_emit_dev(b200cron_ctx* ctx, int dev_index, void* stream, const uint64_t* const masks[6],
+                                 const int32_t* zone_id, const int64_t* earliest, size_t n, const uint64_t* list_off,
+                                 int64_t* list);
+
 /* ---- finished-history ordering + pruning ---------------------------------------------------------------------- */
 
 /* Replaces sortByCreationTimestamp (cron_util.go:117-129) and the prune index rule of syncCronHistory

@@ -1198,3 +1198,28 @@ void orc_batch_history(const uint64_t* seg_off, const int64_t* key, const int64_
   j.which = 2; j.seg_off = seg_off; j.key = key; j.limit = limit; j.perm = perm; j.keep = keep;
   run_jobs(&j, nseg, threads);
 }
+
+/* enumeration of the missed runs themselves (cron_controller.go:409-430 lists nothing; this follows the same chain):
+ * list_off = exclusive prefix sum of min(missed, cap) over Crons whose decision is >= REQUEUE_ONLY, list = those
+ * Crons' first min(missed, cap) fire times.  Returns the total; writes nothing to `list` beyond list_cap. */
+uint64_t orc_batch_unmet_list(const uint64_t* const masks[6], const int32_t* zone_id, const orc_loc* const* locs,
+                              const int64_t* earliest, const uint32_t* missed, const uint8_t* decision, size_t n,
+                              uint32_t cap, uint64_t* list_off, int64_t* list, size_t list_cap) {
+  uint64_t run = 0;
+  for (size_t i = 0; i < n; i++) {
+    list_off[i] = run;
+    uint32_t c = decision[i] >= ORC_DEC_REQUEUE_ONLY ? (missed[i] < cap ? missed[i] : cap) : 0;
+    if (c) {
+      orc_spec s = {masks[0][i], masks[1][i], masks[2][i], masks[3][i], masks[4][i], masks[5][i]};
+      const orc_loc* loc = (zone_id && locs) ? locs[zone_id[i]] : NULL;
+      int64_t t = earliest[i];
+      for (uint32_t j = 0; j < c; j++) {
+        t = orc_spec_next(&s, loc, t);
+        if (run + j < list_cap) list[run + j] = t;
+      }
+    }
+    run += c;
+  }
+  list_off[n] = run;
+  return run;
+}

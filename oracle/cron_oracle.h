@@ -104,6 +104,9 @@ void orc_batch_unmet(const uint64_t* const masks[6], const int32_t* zone_id, con
                      const uint32_t* active, const uint8_t* flags, const int64_t* deadline, size_t n,
                      int64_t* last, int64_t* next, uint32_t* missed, uint8_t* status, uint8_t* decision,
                      int threads);
+uint64_t orc_batch_unmet_list(const uint64_t* const masks[6], const int32_t* zone_id, const orc_loc* const* locs,
+                              const int64_t* earliest, const uint32_t* missed, const uint8_t* decision, size_t n,
+                              uint32_t cap, uint64_t* list_off, int64_t* list, size_t list_cap);
 void orc_batch_history(const uint64_t* seg_off, const int64_t* key, const int64_t* limit, size_t nseg,
                        uint32_t* perm, uint8_t* keep, int threads);
 

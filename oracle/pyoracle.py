@@ -67,6 +67,8 @@ def lib():
         L.orc_batch_unmet.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p,
                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p,
                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        L.orc_batch_unmet_list.restype = C.c_uint64
+        L.orc_batch_unmet_list.argtypes = [C.c_void_p] * 6 + [C.c_size_t, C.c_uint32, C.c_void_p, C.c_void_p, C.c_size_t]
         L.orc_batch_history.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int]
         _LIB = L
     return _LIB
@@ -218,3 +220,19 @@ def batch_history(seg_off, key, limit, threads=None):
     lib().orc_batch_history(seg_off.ctypes.data, key.ctypes.data, _ptr(limit), len(seg_off) - 1, perm.ctypes.data,
                             keep.ctypes.data, threads or cpu_count())
     return perm, keep
+
+
+def batch_unmet_list(masks, earliest, missed, decision, cap, zone_id=None, zone_names=None):
+    n = masks.shape[1]
+    earliest = np.ascontiguousarray(earliest, dtype=np.int64)
+    missed = np.ascontiguousarray(missed, dtype=np.uint32)
+    decision = np.ascontiguousarray(decision, dtype=np.uint8)
+    zid = None if zone_id is None else np.ascontiguousarray(zone_id, dtype=np.int32)
+    planes, locs = _plane_ptrs(masks), _loc_table(zone_names)
+    off = np.empty(n + 1, np.uint64)
+    total = int(np.minimum(missed, cap)[decision >= DEC_REQUEUE_ONLY].sum())
+    lst = np.empty(total, np.int64)
+    got = lib().orc_batch_unmet_list(planes, _ptr(zid), locs, earliest.ctypes.data, missed.ctypes.data,
+                                     decision.ctypes.data, n, cap, off.ctypes.data, lst.ctypes.data, total)
+    assert got == total
+    return off, lst

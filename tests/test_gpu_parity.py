@@ -290,3 +290,52 @@ def test_multi_device_context_matches_single(ctx, names):
         assert np.array_equal(c2.next_n(masks, frm, 4, zid), ctx.next_n(masks, frm, 4, zid))
     finally:
         c2.close()
+
+
+def test_unmet_list_parity(ctx, names):
+    """capped list of the missed fire times: prefix-sum offsets + emit kernel vs the oracle's literal chain"""
+    import torch
+    for n in (1, 5, 1023, 1024, 1025, 50_000):
+        masks = synth.gen_specs(n, seed=52, dense_minutes=0.4)
+        zid = synth.gen_zone_ids(n, len(names), _dst_zones(ctx, names), seed=52)
+        now = ts(2026, 3, 29, 12)
+        earliest = now - synth.gen_times(n, 0, 2 * 86400, seed=52)
+        rng = np.random.default_rng(n)
+        flags = (rng.random(n) < 0.05).astype(np.uint8)
+        u = ctx.unmet_since(masks, earliest, now, flags=flags, zone_id=zid)
+        for cap in (1, 100):
+            off, lst = ctx.unmet_list(masks, earliest, u["missed"], u["decision"], cap, zid)
+            woff, wlst = po.batch_unmet_list(masks, earliest, u["missed"], u["decision"], cap, zid, names)
+            assert np.array_equal(off, woff), (n, cap)
+            assert np.array_equal(lst, wlst), (n, cap)
+            # every listed run is <= now, ascending, and the last listed run of an uncapped Cron is lastMissed
+            cnt = np.diff(off.astype(np.int64))
+            full = (cnt > 0) & (u["missed"] <= cap)
+            ends = off[1:][full].astype(np.int64) - 1
+            assert np.array_equal(lst[ends], u["last"][full])
+    # device-pointer variant, two steps
+    n = 20_000
+    masks = synth.gen_specs(n, seed=53, dense_minutes=0.4)
+    now = ts(2026, 3, 29, 12)
+    earliest = now - synth.gen_times(n, 0, 86400, seed=53)
+    u = ctx.unmet_since(masks, earliest, now)
+    st = torch.cuda.current_stream().cuda_stream
+    dm, de = torch.from_numpy(masks.view(np.int64)).cuda(), torch.from_numpy(earliest).cuda()
+    dmi, dd = torch.from_numpy(u["missed"].view(np.int32)).cuda(), torch.from_numpy(u["decision"]).cuda()
+    doff = torch.empty(n + 1, dtype=torch.int64, device="cuda")
+    ctx.unmet_list_offsets_dev(dmi, dd, doff, 100, stream=st)
+    ctx.sync_check(stream=st)
+    total = int(doff[-1].item())
+    dl = torch.empty(total, dtype=torch.int64, device="cuda")
+    ctx.unmet_list_emit_dev(dm, de, doff, dl, stream=st)
+    ctx.sync_check(stream=st)
+    woff, wlst = po.batch_unmet_list(masks, earliest, u["missed"], u["decision"], 100)
+    assert np.array_equal(doff.cpu().numpy().view(np.uint64), woff) and np.array_equal(dl.cpu().numpy(), wlst)
+    # capacity too small -> ENOMEM with the needed size in list_off[n]
+    with pytest.raises(api.B200CronError) as e:
+        off = np.empty(n + 1, np.uint64)
+        tiny = np.empty(1, np.int64)
+        ctx._check(api.lib().b200cron_unmet_list(ctx._h, api._planes(masks)[0], None, earliest.ctypes.data,
+                                                 u["missed"].ctypes.data, u["decision"].ctypes.data, n, 100,
+                                                 off.ctypes.data, tiny.ctypes.data, 1))
+    assert e.value.code == api.ENOMEM
