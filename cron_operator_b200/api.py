@@ -88,6 +88,8 @@ def lib():
     L.b200cron_unmet_list.argtypes = [vp, vp, vp, vp, vp, vp, sz, C.c_uint32, vp, vp, sz]
     L.b200cron_unmet_list_offsets_dev.restype = i32
     L.b200cron_unmet_list_offsets_dev.argtypes = [vp, i32, vp, vp, vp, sz, C.c_uint32, vp]
+    L.b200cron_unmet_list_offsets_static.restype = i32
+    L.b200cron_unmet_list_offsets_static.argtypes = [vp, i32, vp, vp, vp, sz, C.c_uint32, vp]
     L.b200cron_unmet_list_emit_dev.restype = i32
     L.b200cron_unmet_list_emit_dev.argtypes = [vp, i32, vp, vp, vp, vp, sz, vp, vp]
     L.b200cron_history_prune.restype = i32
@@ -281,6 +283,16 @@ class Context:
     def unmet_list_offsets_dev(self, missed, decision, list_off, cap: int = 100, dev_index: int = 0, stream: int = 0):
         self._check(lib().b200cron_unmet_list_offsets_dev(self._h, dev_index, stream or None, _ptr(missed),
                                                           _ptr(decision), missed.numel(), cap, _ptr(list_off)))
+
+    def unmet_list_offsets_static(self, missed, decision, list_off, cap: int = 100, dev_index: int = 0,
+                                  stream: int = 0, n: int | None = None):
+        """unmet_list_offsets_dev for hosts that must not allocate device memory at call time (a GPU already handed
+        to the host's own pool allocator, or a loop that cannot take cudaMalloc's device-wide sync): the per-tile sums
+        sit in a fixed 128 KiB array inside the library.  At most 16,777,216 Crons per call; calls that overlap on
+        one GPU race on that array.  First call per device resolves the array's address -- do it before capturing."""
+        self._check(lib().b200cron_unmet_list_offsets_static(self._h, dev_index, stream or None, _ptr(missed),
+                                                             _ptr(decision), missed.numel() if n is None else n, cap,
+                                                             _ptr(list_off)))
 
     def unmet_list_emit_dev(self, masks, earliest, list_off, out_list, zone_id=None, dev_index: int = 0, stream: int = 0):
         planes, n = _planes(masks)

@@ -46,6 +46,7 @@ struct Device {
   Slot slots[kSlots];
   uint64_t* d_scratch = nullptr;  // per-tile sums of the unmet-list prefix sum
   size_t scratch_cap = 0;         // entries
+  uint64_t* d_static_sums = nullptr;  // device address of g_static_tile_sums on this device (resolved on first use)
   ZoneTable zt{};
 };
 
@@ -536,6 +537,59 @@ extern "C" int b200cron_unmet_list_offsets_dev(b200cron_ctx* ctx, int dev_index,
   int rc = ensure_scratch(ctx, *d, ntiles + 1);
   if (rc) return rc;
   return launch_list_offsets(ctx, *d, st, missed, decision, n, cap, list_off, d->d_scratch);
+}
+
+
+// -----------------------------------------------------------------------------------------------------------------
+// b200cron_unmet_list_offsets_static: the same prefix sum with its per-tile sums in a fixed device array instead of
+// the context's cudaMalloc'd scratch.
+//
+// Who needs it: hosts that cannot let this library allocate device memory at call time -- a service that hands the
+// whole GPU to its own pool allocator at start-up (a later cudaMalloc fails or fragments that pool), or a reconcile
+// loop that must not run into the device-wide synchronisation cudaMalloc/cudaFree imply while other streams are
+// busy.  b200cron_unmet_list_offsets_dev grows the context's scratch with cudaMalloc whenever n outgrows it; this
+// variant never allocates or frees anything.
+//
+// The array below is reserved on every GPU that loads the library, from module load until the process exits
+// (kStaticTiles + 1 uint64 = 128 KiB + 8 B per GPU).  In host code `g_static_tile_sums` is only a stand-in for the
+// symbol, not a device address -- a kernel handed that name would fault (or, where the GPU can reach host memory,
+// silently use the wrong memory) -- so the entry point resolves the real address once per device with
+// cudaGetSymbolAddress while that device is current, and passes the resolved pointer to the kernels.
+// -----------------------------------------------------------------------------------------------------------------
+namespace {
+constexpr size_t kStaticTiles = 16384;                        // tiles of kScanTile Crons
+constexpr size_t kStaticMaxN = kStaticTiles * (size_t)kScanTile;  // 16,777,216 Crons per call
+static __device__ __align__(256) unsigned long long g_static_tile_sums[kStaticTiles + 1];
+}  // namespace
+
+extern "C" int b200cron_unmet_list_offsets_static(b200cron_ctx* ctx, int dev_index, void* stream,
+                                                  const uint32_t* missed, const uint8_t* decision, size_t n,
+                                                  uint32_t cap, uint64_t* list_off) {
+  Device* d = device_at(ctx, dev_index);
+  if (!d) return B200CRON_EINVAL;
+  if (!missed || !decision || !list_off) return fail(ctx, B200CRON_EINVAL, "unmet_list_offsets_static: NULL argument");
+  if (n > kStaticMaxN)
+    return fail(ctx, B200CRON_EINVAL,
+                "unmet_list_offsets_static: n = %zu exceeds the fixed scratch (at most %zu Crons per call); split the "
+                "batch or use b200cron_unmet_list_offsets_dev",
+                n, kStaticMaxN);
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  CU(ctx, cudaSetDevice(d->id));
+  if (!d->d_static_sums) {
+    // first call on this device: look the array up while this device is current (no allocation involved)
+    void* p = nullptr;
+    CU(ctx, cudaGetSymbolAddress(&p, g_static_tile_sums));
+    d->d_static_sums = static_cast<uint64_t*>(p);
+  }
+  cudaStream_t st = stream ? (cudaStream_t)stream : d->stream;
+  if (n == 0) {
+    CU(ctx, cudaMemsetAsync(list_off, 0, sizeof(uint64_t), st));
+    return B200CRON_OK;
+  }
+  // Nothing in the array has to start at zero: entries [0, ntiles) are written by list_tile_sums_kernel and entry
+  // [ntiles] by list_scan_sums_kernel before anything reads them; whatever an earlier (larger) call left behind in
+  // the entries above ntiles is never read.
+  return launch_list_offsets(ctx, *d, st, missed, decision, n, cap, list_off, d->d_static_sums);
 }
 
 extern "C" int b200cron_unmet_list_emit_dev(b200cron_ctx* ctx, int dev_index, void* stream,

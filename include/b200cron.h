@@ -159,6 +159,21 @@ int b200cron_unmet_list(b200cron_ctx* ctx, const uint64_t* const masks[6], const
  * the caller reads list_off[n] after syncing the stream, then _emit_dev writes the fire times. */
 int b200cron_unmet_list_offsets_dev(b200cron_ctx* ctx, int dev_index, void* stream, const uint32_t* missed,
                                     const uint8_t* decision, size_t n, uint32_t cap, uint64_t* list_off);
+/* No counterpart in the reference (which never touches a GPU): b200cron_unmet_list_offsets_dev for hosts that
+ * cannot let the library allocate device memory while it is being called -- for example a service that gave the whole
+ * GPU to its own pool allocator at start-up, where a later cudaMalloc fails or fragments the pool, or a reconcile
+ * loop that cannot afford the device-wide synchronisation a cudaMalloc/cudaFree causes while other streams are busy.
+ * Same inputs, same list_off output, but the per-tile sums live in a fixed 128 KiB device array that is part of the
+ * library image (every GPU that loads the library holds it until the process exits), so the call never allocates
+ * or frees anything.
+ *  - Limit: n <= 16,777,216 Crons per call; larger n is rejected with B200CRON_EINVAL (split the batch).
+ *  - The first call on each device looks up the array's device address (cudaGetSymbolAddress); make that first
+ *    call before any stream capture begins.
+ *  - Every call on a device shares the one array and finds the previous call's contents in it; each call overwrites
+ *    the entries it reads, so nothing needs clearing, but two calls that overlap on the same GPU (different
+ *    streams, threads or contexts) race on it -- run them one after the other. */
+int b200cron_unmet_list_offsets_static(b200cron_ctx* ctx, int dev_index, void* stream, const uint32_t* missed,
+                                       const uint8_t* decision, size_t n, uint32_t cap, uint64_t* list_off);
 int b200cron_unmet_list_emit_dev(b200cron_ctx* ctx, int dev_index, void* stream, const uint64_t* const masks[6],
                                  const int32_t* zone_id, const int64_t* earliest, size_t n, const uint64_t* list_off,
                                  int64_t* list);
