@@ -254,6 +254,28 @@ struct Walk {
     return x >= ps && x < pe && u >= ps && u < pe;
   }
 
+  // one literal Add(delta) step, 0 < delta <= 3600: inside the period the fields advance with it; across a period
+  // edge they are re-derived from the new offset
+  CW_HD void step(int32_t delta) {
+    const int64_t tn = t + delta;
+    if (tn < pe) {
+      t = tn;
+      sod += delta;
+      if (sod >= 86400) { sod -= 86400; advance_days(1); }
+    } else {
+      load(tn);
+    }
+  }
+  // May an Add-based loop whose field repeats every `modulus` seconds (60 for the second loop, 3600 for the minute
+  // loop) jump from t to tk >= pe?  Yes when tk lies in the very next period and both offsets are congruent modulo
+  // `modulus`: the field then reads the same at every instant of the jump whichever period it falls in.
+  CW_HD bool congruent_across(int64_t tk, int32_t modulus) const {
+    if (pidx < 0 || pidx + 1 >= zn) return false;
+    if (pidx + 2 < zn && tk >= CW_LDG(zw + pidx + 2)) return false;
+    const int32_t o2 = CW_LDG(zo + pidx + 1);
+    return (off % modulus == 0) && (o2 % modulus == 0);
+  }
+
   // move the resident fields forward by k whole days inside the same period (k >= 1, small)
   CW_HD void advance_days(int32_t k) {
     dn += k;
@@ -383,7 +405,7 @@ CW_HD int64_t walk_next(const Spec& s, Walk& w) {
         w.sod += k * 3600;
         if (w.sod >= 86400) { w.sod -= 86400; w.advance_days(1); }
       } else {
-        w.load(w.t + 3600);  // literal step across (or up to) the transition
+        w.step(3600);  // literal step towards / across the transition
       }
       if (w.hour() == 0) { wrapped = true; break; }
     }
@@ -409,8 +431,10 @@ CW_HD int64_t walk_next(const Spec& s, Walk& w) {
         w.t = tk;
         w.sod += k * 60;
         if (w.sod >= 86400) { w.sod -= 86400; w.advance_days(1); }
+      } else if (w.congruent_across(tk, 3600)) {
+        w.load(tk);  // the minute field is blind to a whole-hour offset change: same stopping instant
       } else {
-        w.load(w.t + 60);
+        w.step(60);
       }
       if (w.minute() == 0) { wrapped = true; break; }
     }
@@ -430,8 +454,10 @@ CW_HD int64_t walk_next(const Spec& s, Walk& w) {
         w.t = tk;
         w.sod += k;
         if (w.sod >= 86400) { w.sod -= 86400; w.advance_days(1); }
+      } else if (w.congruent_across(tk, 60)) {
+        w.load(tk);  // the second field is blind to a whole-minute offset change: same stopping instant
       } else {
-        w.load(w.t + 1);
+        w.step(1);
       }
       if (w.second() == 0) { wrapped = true; break; }
     }

@@ -1,0 +1,56 @@
+"""Small driver used for ncu captures of the non-headline kernels:  python profiles/run_kernel.py {unmet|nextn|history} [n]"""
+import sys
+
+import numpy as np
+import torch
+
+sys.path.insert(0, ".")
+from cron_operator_b200 import api, synth  # noqa: E402
+
+which = sys.argv[1]
+n = int(sys.argv[2]) if len(sys.argv) > 2 else 2_000_000
+ctx = api.Context(devices=[0])
+names = ctx.zone_names
+dst = np.array([z for z in range(1, len(names)) if (ctx.zone_periods(z)[0] > synth.ts(2030)).any()])
+stream = torch.cuda.Stream()
+torch.cuda.set_stream(stream)
+st = stream.cuda_stream
+t = lambda a: torch.from_numpy(a).cuda()  # noqa: E731
+ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+if which == "unmet":
+    m = synth.gen_specs(n, seed=41, dense_minutes=0.5)
+    z = synth.gen_zone_ids(n, len(names), dst, seed=41)
+    now = synth.ts(2026, 3, 29, 12)
+    e = now - 30 * 86400 + synth.gen_times(n, -86400, 86400, seed=41)
+    rng = np.random.default_rng(41)
+    dm, dz, de = t(m.view(np.int64)), t(z), t(e)
+    dp, da = t(rng.integers(0, 3, n).astype(np.uint8)), t(rng.choice([0, 1, 2], size=n, p=[.6, .3, .1]).astype(np.uint32))
+    dfl, ddl = t((rng.random(n) < 0.02).astype(np.uint8)), t(np.where(rng.random(n) < 0.01, now - 100, -2**63).astype(np.int64))
+    o = dict(last=torch.empty(n, dtype=torch.int64, device="cuda"), next=torch.empty(n, dtype=torch.int64, device="cuda"),
+             missed=torch.empty(n, dtype=torch.int32, device="cuda"), status=torch.empty(n, dtype=torch.uint8, device="cuda"),
+             decision=torch.empty(n, dtype=torch.uint8, device="cuda"))
+    fn = lambda: ctx.unmet_since_dev(dm, de, now, o, 0, dp, da, dfl, ddl, dz, stream=st)  # noqa: E731
+elif which == "nextn":
+    m = synth.gen_specs(n, seed=3, with_seconds=True)
+    z = synth.gen_zone_ids(n, len(names), dst, seed=3)
+    f = synth.gen_times(n, synth.ts(2024), synth.ts(2036), seed=3)
+    dm, dz, df = t(m.view(np.int64)), t(z), t(f)
+    o = torch.empty((n, 16), dtype=torch.int64, device="cuda")
+    fn = lambda: ctx.next_n_dev(dm, df, o, 16, dz, stream=st)  # noqa: E731
+else:
+    rng = np.random.default_rng(9)
+    lens = rng.integers(0, 17, n)
+    seg = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    key = (1_760_000_000 - rng.integers(0, 86400, int(seg[-1]))).astype(np.int64)
+    ds, dk, dl = t(seg.view(np.int64)), t(key), t(np.full(n, 10, np.int64))
+    perm, keep = torch.empty(len(key), dtype=torch.int32, device="cuda"), torch.empty(len(key), dtype=torch.uint8, device="cuda")
+    fn = lambda: ctx.history_prune_dev(ds, dk, dl, perm, keep, stream=st)  # noqa: E731
+for _ in range(3):
+    fn()
+ctx.sync_check(stream=st)
+ev0.record()
+fn()
+ev1.record()
+ctx.sync_check(stream=st)
+print(which, n, "ms", ev0.elapsed_time(ev1))
+ctx.close()
