@@ -32,6 +32,9 @@
 #ifndef CW_TRACE
 #define CW_TRACE(tag, w)
 #endif
+#ifndef CW_COUNT
+#define CW_COUNT(what)  // host-side instrumentation hook (profiles/); compiles to nothing in the library
+#endif
 
 namespace cronwalk {
 
@@ -322,6 +325,7 @@ CW_HD int64_t walk_next(const Spec& s, Walk& w) {
     int32_t guard = 0;
     while (((s.month >> w.M) & 1u) == 0) {
       CW_TRACE("month", w);
+      CW_COUNT(month_iter);
       if (++guard > kStuck) return kZero;
       if (!added) {
         added = true;
@@ -356,6 +360,7 @@ CW_HD int64_t walk_next(const Spec& s, Walk& w) {
     guard = 0;
     while (!day_matches(s, w.D, w.dn)) {
       CW_TRACE("day", w);
+      CW_COUNT(day_iter);
       if (++guard > kStuck) return kZero;
       if (!added) {
         added = true;
@@ -391,6 +396,7 @@ CW_HD int64_t walk_next(const Spec& s, Walk& w) {
     guard = 0;
     while (((s.hour >> w.hour()) & 1u) == 0) {
       CW_TRACE("hour", w);
+      CW_COUNT(hour_iter);
       if (++guard > kStuck) return kZero;
       if (!added) {
         added = true;
@@ -415,6 +421,7 @@ CW_HD int64_t walk_next(const Spec& s, Walk& w) {
     guard = 0;
     while (((s.minute >> w.minute()) & 1ULL) == 0) {
       CW_TRACE("minute", w);
+      CW_COUNT(minute_iter);
       if (++guard > kStuck) return kZero;
       if (!added) {
         added = true;
@@ -444,6 +451,7 @@ CW_HD int64_t walk_next(const Spec& s, Walk& w) {
     guard = 0;
     while (((s.second >> w.second()) & 1ULL) == 0) {
       CW_TRACE("second", w);
+      CW_COUNT(second_iter);
       if (++guard > kStuck) return kZero;
       added = true;  // Truncate(time.Second) is the identity on whole seconds
       const int32_t sc = w.second();
@@ -600,6 +608,7 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
 // copy of the step emulation: next_try() = t.Add(1s), field decomposition and the closed form; it returns false when
 // only walk_next() can decide (then call next_slow()).  `resident` = w already holds the fields of `t`.
 CW_HD bool next_try(const Spec& s, Walk& w, int64_t t, bool resident, int64_t* out) {
+  CW_COUNT(next);
   if (s.never) { *out = kZero; return true; }
   const int64_t t1 = t + 1;
   if (resident && t1 < w.pe && w.sod + 1 < 86400) {
@@ -610,9 +619,30 @@ CW_HD bool next_try(const Spec& s, Walk& w, int64_t t, bool resident, int64_t* o
   }
   return fast_next(s, w, out);
 }
+// The step emulation is rare and large (thousands of instructions).  On the device it lives out of line, once per
+// kernel image, and takes/returns its state by value so that callers keep their Walk in registers on the fast path
+// (an unmet kernel with it inlined at every call site was 256 KB of SASS and stalled on instruction fetch).
+struct SlowResult {
+  Walk w;
+  int64_t r;
+};
+#if defined(__CUDA_ARCH__)
+__device__ __noinline__
+#else
+inline
+#endif
+SlowResult walk_next_outlined(Spec s, Walk w) {
+  SlowResult x;
+  x.w = w;
+  x.w.lookup(x.w.t);  // fast_next may have moved the period cache; the step emulation wants it on t
+  x.r = walk_next(s, x.w);
+  return x;
+}
 CW_HD int64_t next_slow(const Spec& s, Walk& w) {
-  w.lookup(w.t);  // fast_next may have moved the period cache; the step emulation wants it on t
-  return walk_next(s, w);
+  CW_COUNT(slow);
+  const SlowResult x = walk_next_outlined(s, w);
+  w = x.w;
+  return x.r;
 }
 CW_HD int64_t next_from(const Spec& s, Walk& w, int64_t t, bool resident) {
   int64_t r;

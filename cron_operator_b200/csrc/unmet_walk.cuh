@@ -184,38 +184,49 @@ CW_HD UnmetOut unmet_decide(const Spec& s, const ZoneTable& zt, int32_t zone, co
   Walk w;
   if (zone == 0) w.bind_utc(); else w.bind_zone(zt, zone);
 
-  if (in.earliest > in.now) {  // :404-406
-    o.next = next_from(s, w, in.now, false);
-    o.status = kStEarliestAfterNow;
-    o.decision = kDecRequeueOnly;
-    return o;
-  }
-  // :409  for t := sched.Next(earliest); !t.After(now); t = sched.Next(t)
+  // One loop, one Next() call site (the kernel stays small enough for the instruction cache):
+  //   chain phase  -- :409  for t := sched.Next(earliest); !t.After(now); t = sched.Next(t)
+  //   final phase  -- :405 / :436  sched.Next(now)
   //
   // Upstream bug guard: across a DST overlap a chained Next() can return a time at or before its argument (e.g.
   // Pacific/Chatham: a fire found at 02:59 on the repeated hour makes the next call reset to 02:00 and come back to
   // the first 03:00), and then upstream's loop above cycles forever.  Next() is a pure function of t, so the loop
   // is in a cycle exactly when it revisits a fire time: after every backward step the largest origin is remembered
   // and a fire equal to it ends the call with kStNonTerminating instead of hanging.  No other input is affected.
-  int64_t anchor = kZero;
-  int64_t t = next_from(s, w, in.earliest, false);
-  while (t == kZero || t <= in.now) {
+  const bool after_now = in.earliest > in.now;  // :404-406
+  bool final_phase = after_now;
+  int64_t arg = after_now ? in.now : in.earliest;
+  bool resident = false;
+  int64_t anchor = kZero, prev = kZero;
+  for (;;) {
+    const int64_t t = next_from(s, w, arg, resident);
+    if (final_phase) { o.next = t; break; }
+    if (prev != kZero) {  // t is the Next() of the fire `prev`
+      if (t != kZero && t <= prev && prev > anchor) anchor = prev;
+      if (anchor != kZero && t == anchor) {
+        o.last = kZero; o.missed = 0; o.status = kStNonTerminating; o.decision = kDecErrUnschedulable;
+        return o;
+      }
+    }
     if (t == kZero) {  // :410-412
       o.last = kZero; o.missed = 0; o.status = kStUnschedulable; o.decision = kDecErrUnschedulable;
       return o;
     }
+    if (t > in.now) {  // the chain is over: one more call, from now
+      final_phase = true; arg = in.now; resident = false;
+      continue;
+    }
     o.missed = sat_add(o.missed, 1);
     if (anchor == kZero || w.t > anchor) chain_fast_forward(s, w, in.now, &o.missed);
     o.last = w.t;
-    const int64_t prev = w.t;
-    t = next_from(s, w, prev, true);
-    if (t != kZero && t <= prev && prev > anchor) anchor = prev;
-    if (anchor != kZero && t == anchor) {
-      o.last = kZero; o.missed = 0; o.status = kStNonTerminating; o.decision = kDecErrUnschedulable;
-      return o;
-    }
+    prev = w.t;
+    arg = prev; resident = true;
   }
-  o.next = next_from(s, w, in.now, false);  // :436
+  if (after_now) {
+    o.status = kStEarliestAfterNow;
+    o.decision = kDecRequeueOnly;
+    return o;
+  }
   if (o.last == kZero) o.decision = kDecRequeueOnly;                                        // :196-199
   else if (in.policy == kPolicyForbid && in.active > 0) o.decision = kDecSkipForbid;        // :204-207
   else if (in.policy == kPolicyReplace) o.decision = kDecReplaceCreate;                     // :210-220
