@@ -494,6 +494,42 @@ CW_HD int32_t next_tod_ge(const Spec& s, int32_t sod) {
   return tod;
 }
 
+
+// First fire on the local day `w` is on, at or after local second-of-day `sod` (absolute instant `t`, inside the
+// cached period), allowing the search to cross ONE zone transition.  On success returns true with *r / *rsod set and
+// the period cache on the result.
+//
+// Without a transition in the way this is next_tod_ge().  Across a transition at instant T the Add-based loops keep
+// stepping absolute time while the local fields jump by d = new offset - old offset.  When T falls on a whole local
+// hour, d is a whole number of hours and the local day stays the same, every loop upstream can be in when it reaches
+// T is aligned (minutes and seconds read the same on both sides, the minute loop wraps into a full re-check exactly at
+// T, the hour loop simply continues with the shifted hour), so the walk equals: nothing matched in [sod, local(T)),
+// then the first matching time of day >= local(T) + d in the new period.  Anything else (sub-hour shifts, midnight
+// transitions, no fire left that day) is left to the step emulation.
+CW_HD bool find_tod_today(const Spec& s, Walk& w, int64_t t, int32_t sod, int64_t* r, int32_t* rsod) {
+  const int32_t tod = next_tod_ge(s, sod);
+  if (tod >= 0 && t + (tod - sod) < w.pe) {
+    *r = t + (tod - sod);
+    *rsod = tod;
+    return true;
+  }
+  if (w.pe - t >= 86400 - sod) return false;  // the period outlives the day: no fire left today (tod < 0)
+  if (w.pidx < 0 || w.pidx + 1 >= w.zn) return false;
+  const int32_t sod_t = sod + (int32_t)(w.pe - t);  // local time of day at which the transition strikes (< 86400)
+  const int32_t o2 = CW_LDG(w.zo + w.pidx + 1);
+  const int32_t d = o2 - w.off;
+  const int32_t sod2 = sod_t + d;  // local time of day right after it
+  if (sod_t % 3600 != 0 || d % 3600 != 0 || o2 % 60 != 0 || sod2 < 0 || sod2 >= 86400) return false;
+  const int32_t tod2 = next_tod_ge(s, sod2);
+  if (tod2 < 0) return false;
+  const int64_t rr = w.pe + (tod2 - sod2);
+  if (w.pidx + 2 < w.zn && rr >= CW_LDG(w.zw + w.pidx + 2)) return false;  // a second transition is in the way
+  w.lookup(rr);
+  *r = rr;
+  *rsod = tod2;
+  return true;
+}
+
 // Closed-form Next() from the resident state (t = input + 1s).  Returns true and leaves `w` on the result (or sets
 // *out = kZero) when the answer is provably what upstream's walk produces; returns false -- with w's fields (not
 // its period cache) untouched -- when only the step emulation (walk_next) can tell.
@@ -517,7 +553,6 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
     if (!w.natural((int64_t)w.dn * 86400 + (sod / 3600) * 3600)) return false;  // hour reset Date(Y,M,D,h,0,0)
   }
   const bool month_ok = (s.month >> w.M) & 1u;
-  const int32_t tod = next_tod_ge(s, sod);
   // day mask of the current month, evaluated by every lane before any branch
   bool leap = is_leap(w.Y);
   int32_t first_dn = w.dn - (w.D - 1);
@@ -530,15 +565,17 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
     dm = month_ok ? ((s.star ? (s.dom & dowm) : (s.dom | dowm)) & valid) : 0u;
   }
   const bool today = (dm >> w.D) & 1u;  // == month matches && dayMatches(t)
-  if (today && tod >= 0) {
-    const int64_t r = w.t + (tod - sod);
-    if (r >= w.pe) return false;
-    w.t = r;
-    w.sod = tod;
-    *out = r;
-    return true;
+  if (today) {
+    int64_t r;
+    int32_t rsod;
+    if (find_tod_today(s, w, w.t, sod, &r, &rsod)) {
+      w.t = r;
+      w.sod = rsod;
+      *out = r;
+      return true;
+    }
+    if (w.t + (86400 - sod) >= w.pe) return false;  // the Hour()==0 wrap must happen inside this period
   }
-  if (today && w.t + (86400 - sod) >= w.pe) return false;  // the Hour()==0 wrap must happen inside this period
 
   // ---- calendar search for the next matching day after today, visiting matching months only ----
   const int32_t year_limit = w.Y + 5;
@@ -596,12 +633,20 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
   }
   if (!found) { *out = kZero; return true; }
   if (o % 60 != 0) return false;
-  const int64_t r = u_mid + s.tod1;
-  if (r >= w.pe) return false;
-  w.t = r;
-  w.dn = found_dn; w.sod = s.tod1; w.Y = Yc; w.M = Mc; w.D = Dc;
-  *out = r;
-  return true;
+  // the fire day: Add-based loops run from its midnight (hour 0, minute 0, second 0) to the first fire
+  {
+    const int32_t Ysave = w.Y, Msave = w.M, Dsave = w.D, dnsave = w.dn;
+    int64_t r;
+    int32_t rsod;
+    if (!find_tod_today(s, w, u_mid, 0, &r, &rsod)) {
+      w.Y = Ysave; w.M = Msave; w.D = Dsave; w.dn = dnsave;
+      return false;
+    }
+    w.t = r;
+    w.dn = found_dn; w.sod = rsod; w.Y = Yc; w.M = Mc; w.D = Dc;
+    *out = r;
+    return true;
+  }
 }
 
 // Next(t) in two halves so that kernels can run the straight-line half for several specs in lock step and share one
