@@ -188,36 +188,47 @@ struct UnmetArgs {
 
 __global__ void __launch_bounds__(kUnmetThreads) unmet_kernel(UnmetArgs a, ZoneTable zt, int* __restrict__ err) {
   const size_t i = (size_t)blockIdx.x * kUnmetThreads + threadIdx.x;
-  if (i >= a.n) return;
-  const Spec s = cronwalk::make_spec(__ldg(a.m.p[0] + i), __ldg(a.m.p[1] + i), __ldg(a.m.p[2] + i),
-                                     __ldg(a.m.p[3] + i), __ldg(a.m.p[4] + i), __ldg(a.m.p[5] + i));
+  const bool live = i < a.n;
+  const size_t ii = live ? i : 0;  // out-of-range lanes stay in the warp-uniform loop below, doing nothing
+  const Spec s = cronwalk::make_spec(__ldg(a.m.p[0] + ii), __ldg(a.m.p[1] + ii), __ldg(a.m.p[2] + ii),
+                                     __ldg(a.m.p[3] + ii), __ldg(a.m.p[4] + ii), __ldg(a.m.p[5] + ii));
   cronwalk::UnmetIn in;
-  in.earliest = __ldg(a.earliest + i);
+  in.earliest = __ldg(a.earliest + ii);
   in.now = a.now;
   in.now_nsec = a.now_nsec;
-  in.policy = a.policy ? __ldg(a.policy + i) : 0;
-  in.active = a.active ? __ldg(a.active + i) : 0;
-  in.flags = a.flags ? __ldg(a.flags + i) : 0;
-  in.deadline = a.deadline ? __ldg(a.deadline + i) : kZero;
-  int32_t zone = a.zone_id ? __ldg(a.zone_id + i) : 0;
+  in.policy = a.policy ? __ldg(a.policy + ii) : 0;
+  in.active = a.active ? __ldg(a.active + ii) : 0;
+  in.flags = a.flags ? __ldg(a.flags + ii) : 0;
+  in.deadline = a.deadline ? __ldg(a.deadline + ii) : kZero;
+  const int32_t zone = a.zone_id ? __ldg(a.zone_id + ii) : 0;
 
-  cronwalk::UnmetOut o;
-  o.last = kZero; o.next = kZero; o.missed = 0; o.status = cronwalk::kStOk; o.decision = 0;
-  bool ok = true;
-  const int64_t lo = in.earliest < in.now ? in.earliest : in.now;
-  if (lo < kMinTime || in.now > kMaxTime || in.earliest > kMaxTime) { atomicOr(err, kErrRange); ok = false; }
-  if (ok && zone != 0) {
-    if (zone < 0 || zone >= zt.nzones) { atomicOr(err, kErrZone); ok = false; }
-    else if (__ldg(zt.zstart + zone + 1) - __ldg(zt.zstart + zone) > 1 && in.now >= zt.horizon - kSixYears) {
-      atomicOr(err, kErrRange); ok = false;
+  bool ok = live;
+  if (ok) {
+    const int64_t lo = in.earliest < in.now ? in.earliest : in.now;
+    if (lo < kMinTime || in.now > kMaxTime || in.earliest > kMaxTime) { atomicOr(err, kErrRange); ok = false; }
+    if (ok && zone != 0) {
+      if (zone < 0 || zone >= zt.nzones) { atomicOr(err, kErrZone); ok = false; }
+      else if (__ldg(zt.zstart + zone + 1) - __ldg(zt.zstart + zone) > 1 && in.now >= zt.horizon - kSixYears) {
+        atomicOr(err, kErrRange); ok = false;
+      }
     }
   }
-  if (ok) o = cronwalk::unmet_decide(s, zt, zone, in);
-  a.last[i] = o.last;
-  a.next[i] = o.next;
-  a.missed[i] = o.missed;
-  a.status[i] = o.status;
-  a.decision[i] = o.decision;
+  cronwalk::UnmetState st;
+  st.o.last = kZero; st.o.next = kZero; st.o.missed = 0; st.o.status = cronwalk::kStOk; st.o.decision = 0;
+  st.done = true;
+  st.w.bind_utc();
+  if (ok) cronwalk::unmet_begin(zt, zone, in, st);
+  // all 32 lanes go round together: a full-mask vote per iteration is the reconvergence point
+  while (__any_sync(0xffffffffu, !st.done)) {
+    if (!st.done) cronwalk::unmet_step(s, in, st);
+  }
+  if (live) {
+    a.last[i] = st.o.last;
+    a.next[i] = st.o.next;
+    a.missed[i] = st.o.missed;
+    a.status[i] = st.o.status;
+    a.decision[i] = st.o.decision;
+  }
 }
 
 // -------------------------------------------------------------------------------------------------------------

@@ -170,68 +170,93 @@ CW_HD void chain_fast_forward(const Spec& s, Walk& w, int64_t limit, uint32_t* m
   civil_from_days(last_dn, w.Y, w.M, w.D);
 }
 
-// getNextSchedule + gates + decision for one Cron
-CW_HD UnmetOut unmet_decide(const Spec& s, const ZoneTable& zt, int32_t zone, const UnmetIn& in) {
+// getNextSchedule + gates + decision for one Cron, as a small state machine with ONE Next() call site per step:
+//   chain phase  -- :409  for t := sched.Next(earliest); !t.After(now); t = sched.Next(t)
+//   final phase  -- :405 / :436  sched.Next(now)
+// The kernel drives all 32 lanes of a warp through unmet_step() in lock step (`while (__any_sync(..., !done))`), which
+// makes the lanes reconverge after every call; a plain per-lane loop with early exits left them diverged for good
+// (5 of 32 lanes active) and an inlined Next() per call site made the kernel instruction-fetch bound.
+//
+// Upstream bug guard: across a DST overlap a chained Next() can return a time at or before its argument (e.g.
+// Pacific/Chatham: a fire found at 02:59 on the repeated hour makes the next call reset to 02:00 and come back to
+// the first 03:00), and then upstream's loop above cycles forever.  Next() is a pure function of t, so the loop
+// is in a cycle exactly when it revisits a fire time: after every backward step the largest origin is remembered
+// and a fire equal to it ends the call with kStNonTerminating instead of hanging.  No other input is affected.
+struct UnmetState {
+  Walk w;
   UnmetOut o;
-  o.last = kZero; o.next = kZero; o.missed = 0; o.status = kStOk;
-  if (in.flags & kFlagDeleted) { o.decision = kDecGateDeleted; return o; }
-  if (in.flags & kFlagSuspend) { o.decision = kDecGateSuspended; return o; }
+  int64_t arg, anchor, prev;
+  bool resident, final_phase, after_now, done;
+};
+
+CW_HD void unmet_finish(const UnmetIn& in, UnmetState& st) {
+  st.done = true;
+  if (st.after_now) {
+    st.o.status = kStEarliestAfterNow;
+    st.o.decision = kDecRequeueOnly;
+  } else if (st.o.last == kZero) st.o.decision = kDecRequeueOnly;                            // :196-199
+  else if (in.policy == kPolicyForbid && in.active > 0) st.o.decision = kDecSkipForbid;      // :204-207
+  else if (in.policy == kPolicyReplace) st.o.decision = kDecReplaceCreate;                   // :210-220
+  else st.o.decision = kDecCreate;
+}
+
+CW_HD void unmet_begin(const ZoneTable& zt, int32_t zone, const UnmetIn& in, UnmetState& st) {
+  st.o.last = kZero; st.o.next = kZero; st.o.missed = 0; st.o.status = kStOk; st.o.decision = 0;
+  st.done = true;
+  st.w.bind_utc();
+  if (in.flags & kFlagDeleted) { st.o.decision = kDecGateDeleted; return; }
+  if (in.flags & kFlagSuspend) { st.o.decision = kDecGateSuspended; return; }
   // now.After(deadline): now carries nanoseconds, the deadline is a whole second
   if (in.deadline != kZero && (in.now > in.deadline || (in.now == in.deadline && in.now_nsec > 0))) {
-    o.decision = kDecGateDeadline;
-    return o;
+    st.o.decision = kDecGateDeadline;
+    return;
   }
-  Walk w;
-  if (zone == 0) w.bind_utc(); else w.bind_zone(zt, zone);
+  if (zone != 0) st.w.bind_zone(zt, zone);
+  st.after_now = in.earliest > in.now;  // :404-406
+  st.final_phase = st.after_now;
+  st.arg = st.after_now ? in.now : in.earliest;
+  st.resident = false;
+  st.anchor = kZero;
+  st.prev = kZero;
+  st.done = false;
+}
 
-  // One loop, one Next() call site (the kernel stays small enough for the instruction cache):
-  //   chain phase  -- :409  for t := sched.Next(earliest); !t.After(now); t = sched.Next(t)
-  //   final phase  -- :405 / :436  sched.Next(now)
-  //
-  // Upstream bug guard: across a DST overlap a chained Next() can return a time at or before its argument (e.g.
-  // Pacific/Chatham: a fire found at 02:59 on the repeated hour makes the next call reset to 02:00 and come back to
-  // the first 03:00), and then upstream's loop above cycles forever.  Next() is a pure function of t, so the loop
-  // is in a cycle exactly when it revisits a fire time: after every backward step the largest origin is remembered
-  // and a fire equal to it ends the call with kStNonTerminating instead of hanging.  No other input is affected.
-  const bool after_now = in.earliest > in.now;  // :404-406
-  bool final_phase = after_now;
-  int64_t arg = after_now ? in.now : in.earliest;
-  bool resident = false;
-  int64_t anchor = kZero, prev = kZero;
-  for (;;) {
-    const int64_t t = next_from(s, w, arg, resident);
-    if (final_phase) { o.next = t; break; }
-    if (prev != kZero) {  // t is the Next() of the fire `prev`
-      if (t != kZero && t <= prev && prev > anchor) anchor = prev;
-      if (anchor != kZero && t == anchor) {
-        o.last = kZero; o.missed = 0; o.status = kStNonTerminating; o.decision = kDecErrUnschedulable;
-        return o;
-      }
-    }
-    if (t == kZero) {  // :410-412
-      o.last = kZero; o.missed = 0; o.status = kStUnschedulable; o.decision = kDecErrUnschedulable;
-      return o;
-    }
-    if (t > in.now) {  // the chain is over: one more call, from now
-      final_phase = true; arg = in.now; resident = false;
-      continue;
-    }
-    o.missed = sat_add(o.missed, 1);
-    if (anchor == kZero || w.t > anchor) chain_fast_forward(s, w, in.now, &o.missed);
-    o.last = w.t;
-    prev = w.t;
-    arg = prev; resident = true;
+CW_HD void unmet_step(const Spec& s, const UnmetIn& in, UnmetState& st) {
+  const int64_t t = next_from(s, st.w, st.arg, st.resident);
+  if (st.final_phase) {
+    st.o.next = t;
+    unmet_finish(in, st);
+    return;
   }
-  if (after_now) {
-    o.status = kStEarliestAfterNow;
-    o.decision = kDecRequeueOnly;
-    return o;
+  bool fail = false;
+  uint8_t fail_status = kStUnschedulable;
+  if (st.prev != kZero) {  // t is the Next() of the fire `prev`
+    if (t != kZero && t <= st.prev && st.prev > st.anchor) st.anchor = st.prev;
+    if (st.anchor != kZero && t == st.anchor) { fail = true; fail_status = kStNonTerminating; }
   }
-  if (o.last == kZero) o.decision = kDecRequeueOnly;                                        // :196-199
-  else if (in.policy == kPolicyForbid && in.active > 0) o.decision = kDecSkipForbid;        // :204-207
-  else if (in.policy == kPolicyReplace) o.decision = kDecReplaceCreate;                     // :210-220
-  else o.decision = kDecCreate;
-  return o;
+  if (!fail && t == kZero) fail = true;  // :410-412
+  if (fail) {
+    st.o.last = kZero; st.o.missed = 0; st.o.status = fail_status; st.o.decision = kDecErrUnschedulable;
+    st.done = true;
+    return;
+  }
+  if (t > in.now) {  // the chain is over: one more call, from now
+    st.final_phase = true; st.arg = in.now; st.resident = false;
+    return;
+  }
+  st.o.missed = sat_add(st.o.missed, 1);
+  if (st.anchor == kZero || st.w.t > st.anchor) chain_fast_forward(s, st.w, in.now, &st.o.missed);
+  st.o.last = st.w.t;
+  st.prev = st.w.t;
+  st.arg = st.prev;
+  st.resident = true;
+}
+
+CW_HD UnmetOut unmet_decide(const Spec& s, const ZoneTable& zt, int32_t zone, const UnmetIn& in) {
+  UnmetState st;
+  unmet_begin(zt, zone, in, st);
+  while (!st.done) unmet_step(s, in, st);
+  return st.o;
 }
 
 }  // namespace cronwalk
