@@ -193,14 +193,16 @@ struct Walk {
   int32_t dn;   // local day number
   int32_t sod;  // local second of day
   int32_t Y, M, D;
+  bool today_ok;  // the resident day is known to satisfy the month and day masks (set when a fire was found on it)
 
   CW_HD void bind_utc() {
-    zw = nullptr; zo = nullptr; zf = nullptr; zn = 1; pidx = 0; off = 0; ps = kAlpha; pe = kOmega;
+    zw = nullptr; zo = nullptr; zf = nullptr; zn = 1; pidx = 0; off = 0; ps = kAlpha; pe = kOmega; today_ok = false;
   }
   CW_HD void bind_zone(const ZoneTable& zt, int32_t zone) {
     const int32_t a = CW_LDG(zt.zstart + zone), b = CW_LDG(zt.zstart + zone + 1);
     zw = zt.when + a; zo = zt.off + a; zf = zt.fpre + a; zn = b - a;
     pidx = -1; off = 0; ps = 1; pe = 0;  // empty cache
+    today_ok = false;
     if (zn == 1) { pidx = 0; off = CW_LDG(zo); ps = kAlpha; pe = kOmega; }
   }
 
@@ -240,6 +242,7 @@ struct Walk {
     dn = q;
     sod = r * 128 + (int32_t)(l & 127);
     civil_from_days(dn, Y, M, D);
+    today_ok = false;
   }
 
   // time.Date(y, mo, d, h, mi, s, 0, loc): as-if-UTC seconds, then the two-lookup offset resolution
@@ -281,6 +284,7 @@ struct Walk {
 
   // move the resident fields forward by k whole days inside the same period (k >= 1, small)
   CW_HD void advance_days(int32_t k) {
+    today_ok = false;
     dn += k;
     D += k;
     int32_t dim = days_in_month(Y, M);
@@ -552,6 +556,16 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
     if (w.off % 60 != 0) return false;
     if (!w.natural((int64_t)w.dn * 86400 + (sod / 3600) * 3600)) return false;  // hour reset Date(Y,M,D,h,0,0)
   }
+  if (w.today_ok) {  // chained call on a day already known to match: only the time of day is open
+    int64_t r;
+    int32_t rsod;
+    if (find_tod_today(s, w, w.t, sod, &r, &rsod)) {
+      w.t = r;
+      w.sod = rsod;
+      *out = r;
+      return true;
+    }
+  }
   const bool month_ok = (s.month >> w.M) & 1u;
   // day mask of the current month, evaluated by every lane before any branch
   bool leap = is_leap(w.Y);
@@ -571,6 +585,7 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
     if (find_tod_today(s, w, w.t, sod, &r, &rsod)) {
       w.t = r;
       w.sod = rsod;
+      w.today_ok = true;
       *out = r;
       return true;
     }
@@ -607,6 +622,7 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
     if (!found) { *out = kZero; return true; }
     w.t = x_mid + s.tod1 - w.off;
     w.dn = found_dn; w.sod = s.tod1; w.Y = Yc; w.M = Mc; w.D = Dc;
+    w.today_ok = true;
     *out = w.t;
     return true;
   }
@@ -634,19 +650,14 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
   if (!found) { *out = kZero; return true; }
   if (o % 60 != 0) return false;
   // the fire day: Add-based loops run from its midnight (hour 0, minute 0, second 0) to the first fire
-  {
-    const int32_t Ysave = w.Y, Msave = w.M, Dsave = w.D, dnsave = w.dn;
-    int64_t r;
-    int32_t rsod;
-    if (!find_tod_today(s, w, u_mid, 0, &r, &rsod)) {
-      w.Y = Ysave; w.M = Msave; w.D = Dsave; w.dn = dnsave;
-      return false;
-    }
-    w.t = r;
-    w.dn = found_dn; w.sod = rsod; w.Y = Yc; w.M = Mc; w.D = Dc;
-    *out = r;
-    return true;
-  }
+  int64_t r = u_mid + s.tod1;
+  int32_t rsod = s.tod1;
+  if (r >= w.pe && !find_tod_today(s, w, u_mid, 0, &r, &rsod)) return false;  // a transition sits before the fire
+  w.t = r;
+  w.dn = found_dn; w.sod = rsod; w.Y = Yc; w.M = Mc; w.D = Dc;
+  w.today_ok = true;
+  *out = r;
+  return true;
 }
 
 // Next(t) in two halves so that kernels can run the straight-line half for several specs in lock step and share one
@@ -681,6 +692,7 @@ SlowResult walk_next_outlined(Spec s, Walk w) {
   x.w = w;
   x.w.lookup(x.w.t);  // fast_next may have moved the period cache; the step emulation wants it on t
   x.r = walk_next(s, x.w);
+  x.w.today_ok = false;  // the emulation can end on a day upstream never re-checked
   return x;
 }
 CW_HD int64_t next_slow(const Spec& s, Walk& w) {
