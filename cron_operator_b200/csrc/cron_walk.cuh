@@ -695,16 +695,27 @@ SlowResult walk_next_outlined(Spec s, Walk w) {
   x.w.today_ok = false;  // the emulation can end on a day upstream never re-checked
   return x;
 }
+// kOutline = true: call the single out-of-line copy (unmet / list kernels: several phases share it and the kernel
+// must stay inside the instruction cache); false: inline it (next_n kernels: one call site, and measured faster).
+template <bool kOutline>
 CW_HD int64_t next_slow(const Spec& s, Walk& w) {
   CW_COUNT(slow);
-  const SlowResult x = walk_next_outlined(s, w);
-  w = x.w;
-  return x.r;
+  if (kOutline) {
+    const SlowResult x = walk_next_outlined(s, w);
+    w = x.w;
+    return x.r;
+  }
+  w.lookup(w.t);
+  const int64_t r = walk_next(s, w);
+  w.today_ok = false;
+  return r;
 }
-CW_HD int64_t next_from(const Spec& s, Walk& w, int64_t t, bool resident) {
+template <bool kOutline>
+CW_HD int64_t next_from_t(const Spec& s, Walk& w, int64_t t, bool resident) {
   int64_t r;
   if (next_try(s, w, t, resident, &r)) return r;
-  return next_slow(s, w);
+  return next_slow<kOutline>(s, w);
 }
+CW_HD int64_t next_from(const Spec& s, Walk& w, int64_t t, bool resident) { return next_from_t<false>(s, w, t, resident); }
 
 }  // namespace cronwalk

@@ -53,7 +53,7 @@ constexpr int kNextWarpTile = 64;
 constexpr int kNextTile = kNextWarpTile * (kNextThreads / 32);
 
 template <int KT, bool kVec>
-__global__ void __launch_bounds__(kNextThreads, 10)
+__global__ void __launch_bounds__(kNextThreads, 12)
 next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* __restrict__ from, size_t n, int k_rt,
               int64_t* __restrict__ out, ZoneTable zt, int* __restrict__ err) {
   extern __shared__ __align__(16) int64_t stage_all[];  // [warps][64 * k], unused when KT == 1
@@ -92,48 +92,35 @@ next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* 
     }
   }
 
-  // The lane's two specs run in lock step (unrolled): two independent dependency chains per lane keep the issue
-  // slots busy with fewer resident warps.
+  // The lane's two specs are walked one after the other through ONE copy of the walk in the instruction stream
+  // (operands picked with selects): unrolling both into lock step doubled the code and spilled, and measured slower.
   Spec sp[2];
-  Walk w[2];
-  int64_t t[2];
-  bool ok[2];
 #pragma unroll
-  for (int e = 0; e < 2; ++e) {
-    sp[e] = cronwalk::make_spec(mk[0][e], mk[1][e], mk[2][e], mk[3][e], mk[4][e], mk[5][e]);
-    t[e] = fr[e];
-    ok[e] = (i0 + e < n) && bind_checked(w[e], zt, zz[e], t[e], err);
-  }
+  for (int e = 0; e < 2; ++e) sp[e] = cronwalk::make_spec(mk[0][e], mk[1][e], mk[2][e], mk[3][e], mk[4][e], mk[5][e]);
   const int kk = KT == 1 ? 1 : k;
+  int64_t ra = kZero, rb = kZero;
 #pragma unroll 1
-  for (int j = 0; j < kk; ++j) {
-    bool need[2];
-#pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      need[e] = false;
-      if (ok[e] && t[e] != kZero) need[e] = !cronwalk::next_try(sp[e], w[e], t[e], j > 0, &t[e]);
-      else t[e] = kZero;
-    }
-    if (need[0] | need[1]) {  // rare: a zone transition (or an unnatural Date() target) is in the way
+  for (int e = 0; e < 2; ++e) {
+    if (i0 + e >= n) break;
+    const Spec ss = e ? sp[1] : sp[0];
+    Walk w;
+    int64_t t = e ? fr[1] : fr[0];
+    bool ok = bind_checked(w, zt, e ? zz[1] : zz[0], t, err);
+    const int row = 2 * lane + e;
 #pragma unroll 1
-      for (int e = 0; e < 2; ++e) {
-        if (!(e ? need[1] : need[0])) continue;
-        const Spec ss = e ? sp[1] : sp[0];
-        Walk ww = e ? w[1] : w[0];
-        const int64_t r = cronwalk::next_slow(ss, ww);
-        if (e) { w[1] = ww; t[1] = r; } else { w[0] = ww; t[0] = r; }
+    for (int j = 0; j < kk; ++j) {
+      if (ok && t != kZero) {
+        t = cronwalk::next_from(ss, w, t, j > 0);
+        // chained calls keep walking: re-check the zoned horizon (UTC never trips it)
+        if (KT != 1 && t != kZero && w.zn > 1 && t >= zt.horizon - kSixYears) { atomicOr(err, kErrRange); ok = false; t = kZero; }
+      } else {
+        t = kZero;
       }
+      if (KT > 1) stage[row * KT + ((j + lane) & (KT - 1))] = t;
+      else if (KT == 0) stage[j * kNextWarpTile + row] = t;
     }
-#pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      // chained calls keep walking: re-check the zoned horizon (UTC never trips it)
-      if (KT != 1 && t[e] != kZero && w[e].zn > 1 && t[e] >= zt.horizon - kSixYears) { atomicOr(err, kErrRange); ok[e] = false; t[e] = kZero; }
-      const int row = 2 * lane + e;
-      if (KT > 1) stage[row * KT + ((j + lane) & (KT - 1))] = t[e];
-      else if (KT == 0) stage[j * kNextWarpTile + row] = t[e];
-    }
+    if (e) rb = t; else ra = t;
   }
-  const int64_t ra = t[0], rb = t[1];
 
   if (KT == 1) {
     if (kVec && full) {
@@ -430,7 +417,7 @@ unmet_list_emit_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const 
   int64_t t = __ldg(earliest + i);
   bool resident = false;
   for (uint64_t j = a; j < b; ++j) {
-    t = cronwalk::next_from(s, w, t, resident);
+    t = cronwalk::next_from_t<true>(s, w, t, resident);
     resident = true;
     list[j] = t;
   }

@@ -223,7 +223,7 @@ CW_HD void unmet_begin(const ZoneTable& zt, int32_t zone, const UnmetIn& in, Unm
 }
 
 CW_HD void unmet_step(const Spec& s, const UnmetIn& in, UnmetState& st) {
-  const int64_t t = next_from(s, st.w, st.arg, st.resident);
+  const int64_t t = next_from_t<true>(s, st.w, st.arg, st.resident);
   if (st.final_phase) {
     st.o.next = t;
     unmet_finish(in, st);
