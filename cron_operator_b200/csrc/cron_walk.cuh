@@ -556,29 +556,23 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
     if (w.off % 60 != 0) return false;
     if (!w.natural((int64_t)w.dn * 86400 + (sod / 3600) * 3600)) return false;  // hour reset Date(Y,M,D,h,0,0)
   }
-  if (w.today_ok) {  // chained call on a day already known to match: only the time of day is open
-    int64_t r;
-    int32_t rsod;
-    if (find_tod_today(s, w, w.t, sod, &r, &rsod)) {
-      w.t = r;
-      w.sod = rsod;
-      *out = r;
-      return true;
-    }
-  }
   const bool month_ok = (s.month >> w.M) & 1u;
-  // day mask of the current month, evaluated by every lane before any branch
-  bool leap = is_leap(w.Y);
-  int32_t first_dn = w.dn - (w.D - 1);
   const uint64_t rep = (uint64_t)s.dow * 0x0000000810204081ULL;  // dow pattern repeated every 7 bits
-  uint32_t dm;
-  {
+  bool leap = false;
+  int32_t first_dn = w.dn - (w.D - 1);
+  uint32_t dm = 0;
+  bool have_dm = false;
+  bool today = w.today_ok;  // chained call on a day already known to match: only the time of day is open
+  if (!today) {
+    // day mask of the current month, evaluated by every lane of a fresh call before any branch
+    leap = is_leap(w.Y);
     const int32_t dim = (w.M == 2) ? (leap ? 29 : 28) : 30 + (int32_t)((0x15AAu >> w.M) & 1u);
     const uint32_t valid = (uint32_t)((2ULL << dim) - 2ULL);
     const uint32_t dowm = (uint32_t)((rep >> weekday_of(first_dn)) << 1);
     dm = month_ok ? ((s.star ? (s.dom & dowm) : (s.dom | dowm)) & valid) : 0u;
+    have_dm = true;
+    today = (dm >> w.D) & 1u;  // == month matches && dayMatches(t)
   }
-  const bool today = (dm >> w.D) & 1u;  // == month matches && dayMatches(t)
   if (today) {
     int64_t r;
     int32_t rsod;
@@ -590,6 +584,13 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
       return true;
     }
     if (w.t + (86400 - sod) >= w.pe) return false;  // the Hour()==0 wrap must happen inside this period
+  }
+  if (!have_dm) {
+    leap = is_leap(w.Y);
+    const int32_t dim = (w.M == 2) ? (leap ? 29 : 28) : 30 + (int32_t)((0x15AAu >> w.M) & 1u);
+    const uint32_t valid = (uint32_t)((2ULL << dim) - 2ULL);
+    const uint32_t dowm = (uint32_t)((rep >> weekday_of(first_dn)) << 1);
+    dm = month_ok ? ((s.star ? (s.dom & dowm) : (s.dom | dowm)) & valid) : 0u;
   }
 
   // ---- calendar search for the next matching day after today, visiting matching months only ----

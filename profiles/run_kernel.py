@@ -45,12 +45,16 @@ else:
     ds, dk, dl = t(seg.view(np.int64)), t(key), t(np.full(n, 10, np.int64))
     perm, keep = torch.empty(len(key), dtype=torch.int32, device="cuda"), torch.empty(len(key), dtype=torch.uint8, device="cuda")
     fn = lambda: ctx.history_prune_dev(ds, dk, dl, perm, keep, stream=st)  # noqa: E731
-for _ in range(3):
+reps = int(sys.argv[3]) if len(sys.argv) > 3 else 1
+for _ in range(3 if reps == 1 else 20):  # reps > 1: A/B timing mode, warm the clocks up first
     fn()
 ctx.sync_check(stream=st)
-ev0.record()
-fn()
-ev1.record()
-ctx.sync_check(stream=st)
-print(which, n, "ms", ev0.elapsed_time(ev1))
+best = 1e30
+for _ in range(reps):
+    ev0.record()
+    fn()
+    ev1.record()
+    ctx.sync_check(stream=st)
+    best = min(best, ev0.elapsed_time(ev1))
+print(which, n, "ms", best)
 ctx.close()
