@@ -118,6 +118,11 @@ cudaError_t launch_next(b200cron_ctx* ctx, const Device& d, cudaStream_t st, con
   const unsigned grid = (unsigned)((n + kNextTile - 1) / kNextTile);
   const size_t smem = k == 1 ? 0 : (size_t)kNextTile * k * sizeof(int64_t);
   ctx->launches.fetch_add(1, std::memory_order_relaxed);
+  if (k == 1 && !getenv("B200CRON_NEXT1_PAIRED")) {  // one spec per lane (finer waves); the env var selects the paired kernel
+    next1_kernel<<<(unsigned)((n + kNext1Threads - 1) / kNext1Threads), kNext1Threads, 0, st>>>(m, zone, from, n, out,
+                                                                                               d.zt, d.d_err);
+    return cudaGetLastError();
+  }
   switch (k) {
     case 1: return launch_next_kt<1>(vec, grid, smem, st, m, zone, from, n, k, out, d.zt, d.d_err);
     case 2: return launch_next_kt<2>(vec, grid, smem, st, m, zone, from, n, k, out, d.zt, d.d_err);

@@ -148,6 +148,35 @@ next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* 
   }
 }
 
+
+// -------------------------------------------------------------------------------------------------------------
+// next1: the k == 1 case with ONE spec per lane (64-bit loads, still 256 contiguous bytes per plane per warp).
+// A 1M-spec launch is only ~30 us long: with two specs per lane a resident warp gets ~4.4 tiles and the last,
+// partly filled wave leaves SMs idle for ~20 % of the kernel; halving the tile halves that quantisation loss,
+// which measured as more than the 128-bit loads save.  Used when k == 1; next_n_kernel handles k > 1.
+// -------------------------------------------------------------------------------------------------------------
+#ifndef B200CRON_NEXT1_THREADS
+#define B200CRON_NEXT1_THREADS 64
+#endif
+#ifndef B200CRON_NEXT1_MINBLOCKS
+#define B200CRON_NEXT1_MINBLOCKS 16
+#endif
+constexpr int kNext1Threads = B200CRON_NEXT1_THREADS;
+
+__global__ void __launch_bounds__(kNext1Threads, B200CRON_NEXT1_MINBLOCKS)
+next1_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* __restrict__ from, size_t n,
+             int64_t* __restrict__ out, ZoneTable zt, int* __restrict__ err) {
+  const size_t i = (size_t)blockIdx.x * kNext1Threads + threadIdx.x;
+  if (i >= n) return;
+  const Spec s = cronwalk::make_spec(__ldg(m.p[0] + i), __ldg(m.p[1] + i), __ldg(m.p[2] + i), __ldg(m.p[3] + i),
+                                     __ldg(m.p[4] + i), __ldg(m.p[5] + i));
+  const int64_t t = __ldg(from + i);
+  const int32_t zone = zone_id ? __ldg(zone_id + i) : 0;
+  Walk w;
+  const bool ok = bind_checked(w, zt, zone, t, err);
+  out[i] = ok ? cronwalk::next_from(s, w, t, false) : kZero;
+}
+
 // -------------------------------------------------------------------------------------------------------------
 // unmet_since: getNextSchedule + gates + decision per Cron                    (cron_controller.go:163-220, 389-437)
 // One lane per Cron; every array is read and written with lane-consecutive (coalesced) accesses.
