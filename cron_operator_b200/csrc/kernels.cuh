@@ -261,7 +261,7 @@ __global__ void __launch_bounds__(kUnmetThreads) unmet_kernel(UnmetArgs a, ZoneT
 // -------------------------------------------------------------------------------------------------------------
 constexpr int kHistThreads = 256;
 constexpr int kHistSegs = 256;
-constexpr int kHistCap = 3072;  // records per CTA tile held in shared memory (41 KB static with perm/keep/offsets)
+constexpr int kHistCap = 3072;  // records per CTA tile held in shared memory (44 KB static with perm/keep/seg/offsets)
 
 __global__ void __launch_bounds__(kHistThreads)
 history_prune_kernel(const uint64_t* __restrict__ seg_off, const int64_t* __restrict__ key,
@@ -282,46 +282,60 @@ history_prune_kernel(const uint64_t* __restrict__ seg_off, const int64_t* __rest
     for (uint32_t x = threadIdx.x; x < total; x += kHistThreads) s_key[x] = __ldg(key + r0 + x);
     __syncthreads();
   }
+  if (in_smem) {
+    // Shared-memory path, all 32-bit.  Each segment's thread stamps its id over its own records (segments are
+    // short), so a record finds its segment with one load instead of a binary search over the offsets.
+    __shared__ uint8_t s_seg[kHistCap];
+    __shared__ uint32_t s_rel[kHistSegs + 1];
+    __shared__ int32_t s_lim[kHistSegs];
+    const uint32_t tot = (uint32_t)total;
+    for (int sg = threadIdx.x; sg <= nsegs; sg += kHistThreads) s_rel[sg] = (uint32_t)(s_off[sg] - r0);
+    for (int sg = threadIdx.x; sg < nsegs; sg += kHistThreads) {
+      const int64_t lim = limit ? __ldg(limit + seg0 + sg) : -1;
+      s_lim[sg] = (lim < 0 || lim > (int64_t)kHistCap) ? (int32_t)kHistCap : (int32_t)lim;  // >= len keeps everything
+      const uint32_t a0 = (uint32_t)(s_off[sg] - r0), b0 = (uint32_t)(s_off[sg + 1] - r0);
+      for (uint32_t j = a0; j < b0; ++j) s_seg[j] = (uint8_t)sg;
+    }
+    __syncthreads();
+    for (uint32_t x = threadIdx.x; x < tot; x += kHistThreads) {
+      const int sg = s_seg[x];
+      const uint32_t a = s_rel[sg], b = s_rel[sg + 1];
+      const int64_t kx = s_key[x];
+      uint32_t rank = 0;
+      for (uint32_t j = a; j < b; ++j) {
+        const int64_t kj = s_key[j];
+        rank += (kj < kx) || (kj == kx && j < x);
+      }
+      // sorted position `rank` is deleted when rank < len - limit
+      s_perm[a + rank] = x - a;
+      s_keep[a + rank] = !((int32_t)rank < (int32_t)(b - a) - s_lim[sg]);
+    }
+    __syncthreads();
+    for (uint32_t x = threadIdx.x; x < tot; x += kHistThreads) {
+      perm[r0 + x] = s_perm[x];
+      keep[r0 + x] = s_keep[x];
+    }
+    return;
+  }
+  // Long runs (more than kHistCap records in the tile): rank straight from global memory.
   for (uint64_t x = threadIdx.x; x < total; x += kHistThreads) {
-    // segment of record x: largest sg with s_off[sg] - r0 <= x
-    int lo = 0, hi = nsegs;
+    int lo = 0, hi = nsegs;  // largest sg with s_off[sg] - r0 <= x
     while (hi - lo > 1) {
       const int mid = (lo + hi) >> 1;
       if (s_off[mid] - r0 <= x) lo = mid; else hi = mid;
     }
-    // (empty segments share an offset with their successor; the search lands on the last of them, which owns x)
     const uint64_t a = s_off[lo] - r0, b = s_off[lo + 1] - r0;
     const uint64_t len = b - a;
-    const int64_t kx = in_smem ? s_key[x] : __ldg(key + r0 + x);
+    const int64_t kx = __ldg(key + r0 + x);
     uint32_t rank = 0;
-    if (in_smem) {
-      for (uint64_t j = a; j < b; ++j) {
-        const int64_t kj = s_key[j];
-        rank += (kj < kx) || (kj == kx && j < x);
-      }
-    } else {
-      for (uint64_t j = a; j < b; ++j) {
-        const int64_t kj = __ldg(key + r0 + j);
-        rank += (kj < kx) || (kj == kx && j < x);
-      }
+    for (uint64_t j = a; j < b; ++j) {
+      const int64_t kj = __ldg(key + r0 + j);
+      rank += (kj < kx) || (kj == kx && j < x);
     }
     const int64_t lim = limit ? __ldg(limit + seg0 + lo) : -1;
     // sorted position `rank` is deleted when rank < len - limit (limit < 0: HistoryLimit nil keeps everything)
-    const uint8_t kp = (lim < 0) ? 1 : !((int64_t)rank < (int64_t)len - lim);
-    if (in_smem) {
-      s_perm[a + rank] = (uint32_t)(x - a);
-      s_keep[a + rank] = kp;
-    } else {
-      perm[r0 + a + rank] = (uint32_t)(x - a);
-      keep[r0 + a + rank] = kp;
-    }
-  }
-  if (in_smem) {
-    __syncthreads();
-    for (uint32_t x = threadIdx.x; x < total; x += kHistThreads) {
-      perm[r0 + x] = s_perm[x];
-      keep[r0 + x] = s_keep[x];
-    }
+    perm[r0 + a + rank] = (uint32_t)(x - a);
+    keep[r0 + a + rank] = (lim < 0) ? 1 : !((int64_t)rank < (int64_t)len - lim);
   }
 }
 
