@@ -5,8 +5,8 @@ A "step" is one pass of the hot path over one batch of synthetic specs.  Workloa
 (1M random 5-field UTC cron specs, next single fire time) per GPU (weak scaling: each rank owns its own contiguous
 1M-spec shard of one big synthetic spec list; no collective on the data path).
 
-  value     evals/s with inputs resident in HBM, timed with CUDA events around the kernel on its launch stream,
-            L2 flushed (256 MiB memset) between steps, max over ranks
+  value     evals/s with inputs resident in HBM: K back-to-back steps between one CUDA-event pair on the launch
+            stream; steps rotate through 8 distinct 1M-spec batches (512 MB > L2), max over ranks
   e2e       the same metric through the reference-facing C ABI with pinned HOST buffers (H2D + kernel + D2H inside)
   roofline  algorithmic bytes (64 B/eval) / kernel time vs MEASURED_PEAKS.json hbm_gbs
   cpu_baseline  the C restatement of the reference's Go path (oracle/) on this box's host cores (rank 0, N=1)
@@ -34,6 +34,7 @@ from cron_operator_b200 import synth  # noqa: E402
 N_SPECS = 1_000_000          # C2
 BYTES_PER_EVAL = 64          # 48 masks + 8 from + 8 out
 T_LO, T_HI = synth.ts(2024), synth.ts(2034)
+NCU_TRAFFIC_BYTES = 56_067_072 + 359_424  # one launch of next1_kernel, profiles/r1e_ncu_next1_summary.md
 METRIC = "schedule_evals_per_sec"
 UNIT = "evals/s"
 WORKLOAD = "C2: 1M random 5-field UTC cron specs, next single fire time (per GPU)"
@@ -315,7 +316,10 @@ def main():
                     "ms_per_step": e2e_s / e2e_steps * 1e3, "how": "b200cron_next_n on pinned host buffers, wall clock"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src, "kernel": "next1_kernel",
+                         "traffic": NCU_TRAFFIC_BYTES, "traffic_source": "profiles/r1e_ncu_next1_summary.md "
+                         "(dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full; the 8 MB output "
+                         "is still largely in L2 when the kernel ends)",
+                         "peak_source": peak_src, "kernel": "next1_kernel",
                          "algorithmic_bytes_per_launch": BYTES_PER_EVAL * N_SPECS,
                          "flushed_single_launch_ms_min_med_max": [min(kernel_ms), float(np.median(kernel_ms)), max(kernel_ms)],
                          "note": "cross-check: one launch at a time after a 256 MiB L2 flush, includes launch latency"},
