@@ -375,6 +375,32 @@ class Context:
         return perm[keep == 0], perm[keep == 1]
 
 
+def getDefaultJobName(cron_name: str, schedule_time: int) -> str:
+    """cron_util.go:69-71: fmt.Sprintf("%s-%d", cron.Name, scheduleTime.Unix()) -- the workload is named from nextRun
+    (cron_controller.go:222), which makes duplicate creates collide on AlreadyExists"""
+    return f"{cron_name}-{int(schedule_time)}"
+
+
+def actions_from(result: dict, names, now: int):
+    """Ready-to-apply records for the step right after the path: per Cron the decision,
+    RequeueAfter = next - now (cron_controller.go:192), the workload name for creates (:222, cron_util.go:69-71) and
+    whether Status.LastScheduleTime is set to now (:237)."""
+    out = []
+    for i, name in enumerate(names):
+        d = int(result["decision"][i])
+        nxt = int(result["next"][i])
+        creates = d in (DEC_CREATE, DEC_REPLACE_CREATE)
+        out.append(dict(
+            cron=name, decision=d,
+            requeue_after=(nxt - now) if d >= DEC_REQUEUE_ONLY and nxt != ZERO else None,
+            delete_active=d == DEC_REPLACE_CREATE,
+            create=getDefaultJobName(name, nxt) if creates else None,
+            set_last_schedule_time=now if creates else None,
+            too_many_missed=int(result["missed"][i]) > 100,  # TooManyMissedTimes event, :431-434
+        ))
+    return out
+
+
 class PinnedArray:
     """numpy view over cudaHostAlloc'd memory (b200cron_host_alloc) for the host-pointer calls"""
 

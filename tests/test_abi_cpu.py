@@ -121,3 +121,17 @@ def test_reference_known_answers_parse_side():
     s = api.ParseStandard("*/5 * * * *")  # SURVEY.md 3.4 observed masks
     assert s.masks() == (0x1, 0x0084210842108421, 0x8000000000FFFFFF, 0x80000000FFFFFFFE, 0x8000000000001FFE,
                          0x800000000000007F)
+
+
+def test_K5_default_job_name_and_actions():
+    # cron_util_test.go:137-149: name "cron-test", time Unix(1234567890) -> "cron-test-1234567890"
+    assert api.getDefaultJobName("cron-test", 1234567890) == "cron-test-1234567890"
+    import numpy as np
+    now = 1_767_268_800
+    res = dict(decision=np.array([api.DEC_CREATE, api.DEC_SKIP_FORBID, api.DEC_REPLACE_CREATE, api.DEC_GATE_SUSPENDED]),
+               next=np.array([now + 60, now + 300, now + 5, api.ZERO]), missed=np.array([5, 1, 200, 0]))
+    acts = api.actions_from(res, ["a", "b", "c", "d"], now)
+    assert acts[0]["create"] == f"a-{now + 60}" and acts[0]["requeue_after"] == 60 and acts[0]["set_last_schedule_time"] == now
+    assert acts[1]["create"] is None and acts[1]["requeue_after"] == 300
+    assert acts[2]["delete_active"] and acts[2]["too_many_missed"] and acts[2]["create"] == f"c-{now + 5}"
+    assert acts[3]["requeue_after"] is None and acts[3]["create"] is None
