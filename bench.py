@@ -142,16 +142,38 @@ def extra_kernels(ctx, torch, st, peak):
             best = min(best, e0.elapsed_time(e1))
         return best * 1e-3
 
-    # C3 shape: seconds field, mixed zones, K = 16 (16M specs instead of 100M: 3 GB resident)
-    n, k = 16_000_000, 16
-    masks = synth.gen_specs(n, seed=3, with_seconds=True)
-    zid = synth.gen_zone_ids(n, len(names), dst, seed=3)
-    frm = synth.gen_times(n, synth.ts(2024), synth.ts(2036), seed=3)
-    dm, dz, df = torch.from_numpy(masks.view(np.int64)).cuda(), torch.from_numpy(zid).cuda(), torch.from_numpy(frm).cuda()
+    # C3 at full size: 100M specs with a seconds field, mixed zones, K = 16 -- generated on the device
+    n, k = 100_000_000, 16
+    pool = torch.from_numpy(synth.zone_pool(len(names), dst)).cuda()
+    dm = torch.empty((6, n), dtype=torch.int64, device="cuda")
+    df = torch.empty(n, dtype=torch.int64, device="cuda")
+    dz = torch.empty(n, dtype=torch.int32, device="cuda")
+    ctx.synth_specs_dev(dm, n, 3, 0, True, stream=st)
+    ctx.synth_times_dev(df, n, synth.ts(2024), synth.ts(2036), 3, 0, stream=st)
+    ctx.synth_zones_dev(dz, n, pool, 3, 0, stream=st)
     o = torch.empty((n, k), dtype=torch.int64, device="cuda")
-    s = timed(lambda: ctx.next_n_dev(dm, df, o, k, dz, stream=st))
-    out["C3_nextN_k16_zoned"] = {"specs": n, "evals_per_s": n * k / s, "specs_per_s": n / s, "ms": s * 1e3,
-                                 "bytes_per_spec": 188, "roofline_frac": 188 * n / s / 1e9 / peak}
+    s = timed(lambda: ctx.next_n_dev(dm, df, o, k, dz, stream=st), reps=3)
+    out["C3_nextN_k16_zoned_100M"] = {"specs": n, "evals_per_s": n * k / s, "specs_per_s": n / s, "ms": s * 1e3,
+                                      "bytes_per_spec": 188, "roofline_frac": 188 * n / s / 1e9 / peak,
+                                      "data": "generated on device (b200cron_synth_*_dev), seed 3"}
+    del o
+    # C5 evaluation part on one GPU: 1B UTC specs, next fire (64 GB resident) when the device has the room
+    try:
+        if torch.cuda.mem_get_info()[0] > 90 * (1 << 30):
+            del dm, df, dz
+            n5 = 1_000_000_000
+            dm5 = torch.empty((6, n5), dtype=torch.int64, device="cuda")
+            df5 = torch.empty(n5, dtype=torch.int64, device="cuda")
+            ctx.synth_specs_dev(dm5, n5, 0xC0FFEE, 0, False, stream=st)
+            ctx.synth_times_dev(df5, n5, T_LO, T_HI, 0xC0FFEE, 0, stream=st)
+            o5 = torch.empty((n5, 1), dtype=torch.int64, device="cuda")
+            s = timed(lambda: ctx.next_n_dev(dm5, df5, o5, 1, None, stream=st), reps=3)
+            out["C5_eval_part_1B_specs"] = {"specs": n5, "evals_per_s": n5 / s, "ms": s * 1e3,
+                                            "roofline_frac": 64 * n5 / s / 1e9 / peak}
+            del dm5, df5, o5
+    except Exception as e:
+        out["C5_eval_part_1B_specs"] = {"error": repr(e)}
+    torch.cuda.empty_cache()
     # C4 shape: unmet + decision, 30-day backlog, now inside a European DST day
     n4 = 10_000_000
     m4 = synth.gen_specs(n4, seed=41, dense_minutes=0.5)
@@ -172,7 +194,7 @@ def extra_kernels(ctx, torch, st, peak):
                              "roofline_frac": 96 * n4 / s / 1e9 / peak, "missed_runs_counted": missed_total,
                              "equivalent_literal_next_calls_per_s": (missed_total + 2 * n4) / s,
                              "note": "missed runs are counted analytically; not literal Next() calls"}
-    del dm, dz, df, o, dm4, dz4, de4, o4
+    del dm4, dz4, de4, o4
     # C5 shape: history sort/prune, U{0..16} records per Cron, historyLimit 10 (8M segments)
     ns = 8_000_000
     lens = rng.integers(0, 17, ns)

@@ -96,6 +96,12 @@ def lib():
     L.b200cron_history_prune.argtypes = [vp, vp, vp, vp, sz, vp, vp]
     L.b200cron_history_prune_dev.restype = i32
     L.b200cron_history_prune_dev.argtypes = [vp, i32, vp, vp, vp, vp, sz, sz, vp, vp]
+    L.b200cron_synth_specs_dev.restype = i32
+    L.b200cron_synth_specs_dev.argtypes = [vp, i32, vp, C.c_uint64, C.c_uint64, sz, i32, C.c_double, C.c_double, vp, vp]
+    L.b200cron_synth_times_dev.restype = i32
+    L.b200cron_synth_times_dev.argtypes = [vp, i32, vp, C.c_uint64, C.c_uint64, sz, i64, i64, C.c_uint64, vp]
+    L.b200cron_synth_zones_dev.restype = i32
+    L.b200cron_synth_zones_dev.argtypes = [vp, i32, vp, C.c_uint64, C.c_uint64, sz, vp, sz, C.c_double, vp]
     L.b200cron_sync_check.restype = i32
     L.b200cron_sync_check.argtypes = [vp, i32, vp]
     L.b200cron_launch_count.restype = C.c_uint64
@@ -328,6 +334,25 @@ class Context:
         nseg = seg_off.numel() - 1
         self._check(lib().b200cron_history_prune_dev(self._h, dev_index, stream or None, _ptr(seg_off), _ptr(key),
                                                      _ptr(limit), nseg, key.numel(), _ptr(perm), _ptr(keep)))
+
+    # ---- device-side synthetic workloads (bit-identical to synth.py)
+    def synth_specs_dev(self, masks_out, n: int, seed: int = 0xC0FFEE, start: int = 0, with_seconds: bool = False,
+                        dense_minutes: float = 0.0, plant_unschedulable: float = 0.001, dev_index: int = 0, stream: int = 0):
+        from . import synth
+        th = np.concatenate([synth.form_thresholds(0.40), synth.form_thresholds(0.60)]).astype(np.float64)
+        planes, _ = _planes(masks_out)
+        self._check(lib().b200cron_synth_specs_dev(self._h, dev_index, stream or None, seed, start, n, int(with_seconds),
+                                                   dense_minutes, plant_unschedulable, th.ctypes.data, planes))
+
+    def synth_times_dev(self, out, n: int, lo: int, hi: int, seed: int = 0xC0FFEE, start: int = 0, stream_id: int = 200,
+                        dev_index: int = 0, stream: int = 0):
+        self._check(lib().b200cron_synth_times_dev(self._h, dev_index, stream or None, seed, start, n, lo, hi, stream_id,
+                                                   _ptr(out)))
+
+    def synth_zones_dev(self, out, n: int, pool, seed: int = 0xC0FFEE, start: int = 0, p_utc: float = 0.5,
+                        dev_index: int = 0, stream: int = 0):
+        self._check(lib().b200cron_synth_zones_dev(self._h, dev_index, stream or None, seed, start, n, _ptr(pool),
+                                                   pool.numel(), p_utc, _ptr(out)))
 
     def sync_check(self, dev_index: int = 0, stream: int = 0):
         self._check(lib().b200cron_sync_check(self._h, dev_index, stream or None))

@@ -17,6 +17,7 @@
 
 #include "../../include/b200cron.h"
 #include "kernels.cuh"
+#include "synth_kernels.cuh"
 #include "zone_table.h"
 
 namespace {
@@ -735,5 +736,58 @@ extern "C" int b200cron_history_prune(b200cron_ctx* ctx, const uint64_t* seg_off
     CU(ctx, cudaSetDevice(d.id));
     CU(ctx, cudaStreamSynchronize(d.slots[0].stream));
   }
+  return B200CRON_OK;
+}
+
+// =================================================================================================================
+// synthetic workloads (bench / test support)
+// =================================================================================================================
+extern "C" int b200cron_synth_specs_dev(b200cron_ctx* ctx, int dev_index, void* stream, uint64_t seed, uint64_t start,
+                                        size_t n, int with_seconds, double dense_minutes, double plant_unschedulable,
+                                        const double thresholds[10], uint64_t* const masks_out[6]) {
+  Device* d = device_at(ctx, dev_index);
+  if (!d) return B200CRON_EINVAL;
+  if (!thresholds || !masks_out) return fail(ctx, B200CRON_EINVAL, "synth_specs: NULL argument");
+  if (n == 0) return B200CRON_OK;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  CU(ctx, cudaSetDevice(d->id));
+  SynthThresholds th;
+  for (int q = 0; q < 5; ++q) { th.t[0][q] = thresholds[q]; th.t[1][q] = thresholds[5 + q]; }
+  SynthPlanes out;
+  for (int p = 0; p < 6; ++p) out.p[p] = masks_out[p];
+  ctx->launches.fetch_add(1, std::memory_order_relaxed);
+  synth_specs_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream ? (cudaStream_t)stream : d->stream>>>(
+      seed, start, n, with_seconds, dense_minutes, plant_unschedulable, th, out);
+  CU(ctx, cudaGetLastError());
+  return B200CRON_OK;
+}
+
+extern "C" int b200cron_synth_times_dev(b200cron_ctx* ctx, int dev_index, void* stream, uint64_t seed, uint64_t start,
+                                        size_t n, int64_t lo, int64_t hi, uint64_t stream_id, int64_t* out) {
+  Device* d = device_at(ctx, dev_index);
+  if (!d) return B200CRON_EINVAL;
+  if (!out || hi <= lo) return fail(ctx, B200CRON_EINVAL, "synth_times: bad argument");
+  if (n == 0) return B200CRON_OK;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  CU(ctx, cudaSetDevice(d->id));
+  ctx->launches.fetch_add(1, std::memory_order_relaxed);
+  synth_times_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream ? (cudaStream_t)stream : d->stream>>>(
+      seed, start, n, lo, hi, stream_id, out);
+  CU(ctx, cudaGetLastError());
+  return B200CRON_OK;
+}
+
+extern "C" int b200cron_synth_zones_dev(b200cron_ctx* ctx, int dev_index, void* stream, uint64_t seed, uint64_t start,
+                                        size_t n, const int32_t* pool, size_t pool_len, double p_utc, int32_t* out) {
+  Device* d = device_at(ctx, dev_index);
+  if (!d) return B200CRON_EINVAL;
+  if (!out || !pool || pool_len == 0) return fail(ctx, B200CRON_EINVAL, "synth_zones: bad argument");
+  if (n == 0) return B200CRON_OK;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  CU(ctx, cudaSetDevice(d->id));
+  ctx->launches.fetch_add(1, std::memory_order_relaxed);
+  synth_zones_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream ? (cudaStream_t)stream : d->stream>>>(
+      seed, start, n, pool, pool_len, p_utc, out);
+  CU(ctx, cudaGetLastError());
   return B200CRON_OK;
 }

@@ -36,15 +36,21 @@ def _uniform_int(r: np.ndarray, lo, hi) -> np.ndarray:
     return (r % span).astype(np.int64) + lo
 
 
+def form_thresholds(p_star: float) -> np.ndarray:
+    """the 5 cumulative thresholds that split u in [0,1) into the 6 field forms (also handed to the device generator,
+    so that both sides compare against the very same doubles)"""
+    rest = 1.0 - p_star
+    cuts = p_star + rest * np.array([0.25, 0.25 + 0.3333, 0.25 + 0.3333 + 0.1667, 0.25 + 0.3333 + 0.1667 + 0.0833])
+    return np.concatenate(([p_star], cuts)).astype(np.float64)
+
+
 def gen_field(seed: int, idx: np.ndarray, field: int, p_star: float = 0.40) -> np.ndarray:
     """One mask per index.  Forms: `*` p_star, `*/k` 15%, single 20%, `a-b` 10%, `a-b/k` 5%, list of 2-4 rest."""
     lo, hi = BOUNDS[field]
     n = idx.shape[0]
     base = field * 16
     u = (_draw(seed, idx, base + 0) >> U64(11)).astype(np.float64) / float(1 << 53)
-    rest = 1.0 - p_star
-    cuts = p_star + rest * np.array([0.25, 0.25 + 0.3333, 0.25 + 0.3333 + 0.1667, 0.25 + 0.3333 + 0.1667 + 0.0833])
-    form = np.searchsorted(np.concatenate(([p_star], cuts)), u, side="right")  # 0 star,1 */k,2 single,3 a-b,4 a-b/k,5 list
+    form = np.searchsorted(form_thresholds(p_star), u, side="right")  # 0 star,1 */k,2 single,3 a-b,4 a-b/k,5 list
     span = hi - lo + 1
     kmax = max(2, span // 2)
     k = _uniform_int(_draw(seed, idx, base + 1), 2, kmax)
@@ -69,9 +75,12 @@ def gen_field(seed: int, idx: np.ndarray, field: int, p_star: float = 0.40) -> n
 
 
 def gen_specs(n: int, seed: int = 0xC0FFEE, start: int = 0, with_seconds: bool = False, dense_minutes: float = 0.0,
-              plant_unschedulable: float = 0.001) -> np.ndarray:
-    """(6, n) uint64 SoA mask planes for spec indices [start, start + n)."""
-    idx = np.arange(start, start + n, dtype=np.uint64)
+              plant_unschedulable: float = 0.001, idx: np.ndarray | None = None) -> np.ndarray:
+    """(6, n) uint64 SoA mask planes for spec indices [start, start + n), or for the explicit index array `idx`."""
+    if idx is None:
+        idx = np.arange(start, start + n, dtype=np.uint64)
+    idx = np.asarray(idx, dtype=np.uint64)
+    n = len(idx)
     m = np.empty((6, n), dtype=np.uint64)
     m[0] = gen_field(seed, idx, 0) if with_seconds else U64(1)
     m[1] = gen_field(seed, idx, 1)
@@ -102,17 +111,27 @@ def gen_specs(n: int, seed: int = 0xC0FFEE, start: int = 0, with_seconds: bool =
     return np.ascontiguousarray(m)
 
 
-def gen_times(n: int, lo: int, hi: int, seed: int = 0xC0FFEE, start: int = 0, stream: int = 200) -> np.ndarray:
-    idx = np.arange(start, start + n, dtype=np.uint64)
+def gen_times(n: int, lo: int, hi: int, seed: int = 0xC0FFEE, start: int = 0, stream: int = 200,
+              idx: np.ndarray | None = None) -> np.ndarray:
+    if idx is None:
+        idx = np.arange(start, start + n, dtype=np.uint64)
+    idx = np.asarray(idx, dtype=np.uint64)
+    n = len(idx)
     return _uniform_int(_draw(seed, idx, stream), lo, np.full(n, hi - 1)).astype(np.int64)
 
 
+def zone_pool(nzones: int, dst_zone_ids: np.ndarray) -> np.ndarray:
+    return np.concatenate([np.arange(1, nzones, dtype=np.int32), np.asarray(dst_zone_ids, dtype=np.int32)])
+
+
 def gen_zone_ids(n: int, nzones: int, dst_zone_ids: np.ndarray, seed: int = 0xC0FFEE, start: int = 0,
-                 p_utc: float = 0.5) -> np.ndarray:
+                 p_utc: float = 0.5, idx: np.ndarray | None = None) -> np.ndarray:
     """C3: 50% UTC (id 0), the rest uniform over zones 1..nzones-1 with DST-rule zones double-weighted."""
-    idx = np.arange(start, start + n, dtype=np.uint64)
+    if idx is None:
+        idx = np.arange(start, start + n, dtype=np.uint64)
+    idx = np.asarray(idx, dtype=np.uint64)
     u = (_draw(seed, idx, 300) >> U64(11)).astype(np.float64) / float(1 << 53)
-    pool = np.concatenate([np.arange(1, nzones, dtype=np.int32), np.asarray(dst_zone_ids, dtype=np.int32)])
+    pool = zone_pool(nzones, dst_zone_ids)
     pick = pool[(_draw(seed, idx, 301) % U64(len(pool))).astype(np.int64)]
     return np.where(u < p_utc, 0, pick).astype(np.int32)
 

@@ -192,6 +192,19 @@ int b200cron_history_prune_dev(b200cron_ctx* ctx, int dev_index, void* stream, c
                                const int64_t* key, const int64_t* limit, size_t nseg, size_t nrec, uint32_t* perm,
                                uint8_t* keep);
 
+/* ---- synthetic workloads (benchmark / test support; no counterpart in the reference) ---------------------------
+ * Device-side generators of the BASELINE.json workloads, bit-identical to cron_operator_b200/synth.py: every draw is
+ * a counter-based hash of (seed, index, stream), so shards can be generated where they are consumed and any index
+ * can be regenerated on the host for sampled parity.  `thresholds` = the ten doubles of synth.form_thresholds(0.40)
+ * followed by synth.form_thresholds(0.60); outputs are device pointers on device dev_index. */
+int b200cron_synth_specs_dev(b200cron_ctx* ctx, int dev_index, void* stream, uint64_t seed, uint64_t start, size_t n,
+                             int with_seconds, double dense_minutes, double plant_unschedulable,
+                             const double thresholds[10], uint64_t* const masks_out[6]);
+int b200cron_synth_times_dev(b200cron_ctx* ctx, int dev_index, void* stream, uint64_t seed, uint64_t start, size_t n,
+                             int64_t lo, int64_t hi, uint64_t stream_id, int64_t* out);
+int b200cron_synth_zones_dev(b200cron_ctx* ctx, int dev_index, void* stream, uint64_t seed, uint64_t start, size_t n,
+                             const int32_t* pool, size_t pool_len, double p_utc, int32_t* out);
+
 /* `_dev` calls only enqueue work: this waits for `stream` (NULL = the context's stream) on device dev_index and
  * reports what the kernels flagged since the last check (B200CRON_ERANGE for out-of-range times / zone ids). */
 int b200cron_sync_check(b200cron_ctx* ctx, int dev_index, void* stream);

@@ -339,3 +339,61 @@ def test_unmet_list_parity(ctx, names):
                                                  u["missed"].ctypes.data, u["decision"].ctypes.data, n, 100,
                                                  off.ctypes.data, tiny.ctypes.data, 1))
     assert e.value.code == api.ENOMEM
+
+
+def test_device_generator_matches_numpy(ctx, names):
+    """the device-side synthetic workload generator is bit-identical to synth.py for any index window"""
+    import torch
+    st = torch.cuda.current_stream().cuda_stream
+    dst = _dst_zones(ctx, names)
+    pool = torch.from_numpy(synth.zone_pool(len(names), dst)).cuda()
+    for (n, start, ws, dense, seed) in [(100_003, 0, False, 0.0, 0xC0FFEE), (65_537, 987_654_321, True, 0.0, 3),
+                                         (50_000, 123, False, 0.5, 41)]:
+        dm = torch.empty((6, n), dtype=torch.int64, device="cuda")
+        df = torch.empty(n, dtype=torch.int64, device="cuda")
+        dz = torch.empty(n, dtype=torch.int32, device="cuda")
+        ctx.synth_specs_dev(dm, n, seed, start, ws, dense, 0.001, stream=st)
+        ctx.synth_times_dev(df, n, ts(2024), ts(2036), seed, start, stream=st)
+        ctx.synth_zones_dev(dz, n, pool, seed, start, stream=st)
+        ctx.sync_check(stream=st)
+        assert np.array_equal(dm.cpu().numpy().view(np.uint64), synth.gen_specs(n, seed, start, ws, dense)), (n, start)
+        assert np.array_equal(df.cpu().numpy(), synth.gen_times(n, ts(2024), ts(2036), seed, start))
+        assert np.array_equal(dz.cpu().numpy(), synth.gen_zone_ids(n, len(names), dst, seed, start))
+    # index-array regeneration used for sampled parity at full size
+    idx = np.array([5, 77, 100_002], dtype=np.uint64)
+    assert np.array_equal(synth.gen_specs(0, idx=idx), synth.gen_specs(100_003)[:, idx.astype(np.int64)])
+
+
+def test_C3_full_size_sampled_parity(ctx, names):
+    """BASELINE config 3 at its full size: 100M specs with a seconds field and mixed IANA zones generated on the
+    device, next 16 fire times each; oracle parity on every 9973rd index (regenerated on the host by index) plus the
+    size-independent row properties over all 1.6e9 results."""
+    import torch
+    free, _ = torch.cuda.mem_get_info()
+    n, k = 100_000_000, 16
+    if free < 30 * (1 << 30):
+        pytest.skip("needs ~20 GB of free device memory")
+    st = torch.cuda.current_stream().cuda_stream
+    dst = _dst_zones(ctx, names)
+    pool = torch.from_numpy(synth.zone_pool(len(names), dst)).cuda()
+    dm = torch.empty((6, n), dtype=torch.int64, device="cuda")
+    df = torch.empty(n, dtype=torch.int64, device="cuda")
+    dz = torch.empty(n, dtype=torch.int32, device="cuda")
+    ctx.synth_specs_dev(dm, n, 3, 0, True, stream=st)
+    ctx.synth_times_dev(df, n, ts(2024), ts(2036), 3, 0, stream=st)
+    ctx.synth_zones_dev(dz, n, pool, 3, 0, stream=st)
+    out = torch.empty((n, k), dtype=torch.int64, device="cuda")
+    ctx.next_n_dev(dm, df, out, k, dz, stream=st)
+    ctx.sync_check(stream=st)
+    idx = np.arange(0, n, 9973, dtype=np.uint64)
+    want = po.batch_next_n(synth.gen_specs(0, 3, with_seconds=True, idx=idx), synth.gen_times(0, ts(2024), ts(2036), 3, idx=idx),
+                           k, synth.gen_zone_ids(0, len(names), dst, 3, idx=idx), names)
+    got = out[torch.from_numpy(idx.astype(np.int64)).cuda()].cpu().numpy()
+    bad = np.nonzero((got != want).any(axis=1))[0]
+    assert len(bad) == 0, (idx[bad][:5], got[bad[:2]], want[bad[:2]])
+    zero = out == po.ZERO
+    assert bool((zero[:, 1:] | ~zero[:, :-1]).all())        # once the zero time, always the zero time
+    assert bool(((out[:, 0] > df) | zero[:, 0]).all())      # first fire is after `from`
+    # rows increase except where upstream itself steps back across a DST overlap (DESIGN.md section 2): rare
+    back = ((out[:, 1:] <= out[:, :-1]) & ~zero[:, 1:]).sum().item()
+    assert back < n * k * 1e-6, back
