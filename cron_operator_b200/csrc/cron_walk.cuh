@@ -58,6 +58,7 @@ struct ZoneTable {
 struct Spec {  // sanitised masks: only the bits upstream can test are kept
   uint64_t second, minute;
   uint32_t hour, dom, month, dow;
+  uint32_t month_eff;  // month mask minus the months that can never hold a matching day (closed form only)
   bool star;   // Dom&starBit || Dow&starBit  -> AND rule, else OR rule (spec.go dayMatches)
   bool never;  // some field can never match: upstream walks to the 5-year limit and returns the zero time
   int32_t tod1;     // first matching second of day (first hour, first minute, first second); valid when !never
@@ -78,6 +79,15 @@ CW_HD Spec make_spec(uint64_t second, uint64_t minute, uint64_t hour, uint64_t d
   s.dow = (uint32_t)(dow & 0x7Fu);
   s.star = ((dom | dow) >> 63) != 0;
   const bool no_day = s.star ? (s.dom == 0 || s.dow == 0) : (s.dom == 0 && s.dow == 0);
+  // Months in which no day can match: when the day-of-month mask decides alone (AND rule, or OR rule with an empty
+  // day-of-week mask), a 30-day month needs a dom bit <= 30 and February one <= 29.  With a non-empty day-of-week
+  // mask under the OR rule every month matches (each weekday occurs in any 28 days).  The step emulation keeps the
+  // original mask: it walks such months day by day, as upstream does.
+  s.month_eff = s.month;
+  if (s.star || s.dow == 0) {
+    if ((s.dom & 0x7FFFFFFEu) == 0) s.month_eff &= ~((1u << 4) | (1u << 6) | (1u << 9) | (1u << 11));
+    if ((s.dom & 0x3FFFFFFEu) == 0) s.month_eff &= ~(1u << 2);
+  }
   // first set positions with a sentinel bit above the valid range: an empty mask shows up as the sentinel
   const int32_t fs = ctz64(s.second | (1ULL << 60)), fm = ctz64(s.minute | (1ULL << 60)), fh = ctz32(s.hour | (1u << 24));
   s.never = (fs == 60) | (fm == 60) | (fh == 24) | (s.month == 0) | no_day;
@@ -598,17 +608,20 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
   int32_t Yc = w.Y, Mc = w.M;
   int32_t jan1 = first_dn - days_before_month(Mc) - ((leap && Mc > 2) ? 1 : 0);
   dm &= ~((2u << w.D) - 1u);  // current month: days after today
+  CW_COUNT(cal_enter);
   while (dm == 0) {
-    const uint32_t later = s.month & ~((2u << Mc) - 1u);
+    CW_COUNT(cal_iter);
+    const uint32_t later = s.month_eff & ~((2u << Mc) - 1u);
     if (later) {
       Mc = ctz32(later);
     } else {
       jan1 += 365 + (leap ? 1 : 0);
       ++Yc;
       leap = is_leap(Yc);
-      Mc = ctz32(s.month);
+      Mc = ctz32(s.month_eff | (1u << 13));  // 13: no month can ever match -> only the year counter advances
       if (Yc > year_limit) break;
     }
+    if (Mc > 12) continue;
     first_dn = jan1 + days_before_month(Mc) + ((leap && Mc > 2) ? 1 : 0);
     const int32_t dim = (Mc == 2) ? (leap ? 29 : 28) : 30 + (int32_t)((0x15AAu >> Mc) & 1u);
     const uint32_t valid = (uint32_t)((2ULL << dim) - 2ULL);
