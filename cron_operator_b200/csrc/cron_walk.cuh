@@ -187,30 +187,6 @@ CW_HD int32_t weekday_of(int32_t dn) {  // Sunday = 0; 1970-01-01 was a Thursday
   return (int32_t)(((uint32_t)(dn + 4 + 1073741823)) % 7u);
 }
 
-// Period search of Walk::lookup on a cache miss: largest i with when[i] <= x (when[0] == kAlpha).  Transitions are
-// usually crossed one at a time, so the neighbours of the cached period are tried before the binary search.
-#if defined(__CUDA_ARCH__)
-__device__ __noinline__
-#else
-inline
-#endif
-void lookup_miss(const int64_t* zw, const int32_t* zo, int32_t zn, int32_t pidx, bool above, int64_t x,
-                 int32_t& o_idx, int32_t& o_off, int64_t& o_ps, int64_t& o_pe) {
-  int32_t lo = 0, hi = zn;
-  if (pidx >= 0) {
-    if (above) { lo = pidx + 1; if (lo + 1 >= zn || x < CW_LDG(zw + lo + 1)) hi = lo + 1; }
-    else { hi = pidx; if (hi - 1 >= 0 && x >= CW_LDG(zw + hi - 1)) lo = hi - 1; }
-  }
-  while (hi - lo > 1) {
-    const int32_t mid = (int32_t)((uint32_t)(lo + hi) >> 1);
-    if (x < CW_LDG(zw + mid)) hi = mid; else lo = mid;
-  }
-  o_idx = lo;
-  o_off = CW_LDG(zo + lo);
-  o_ps = CW_LDG(zw + lo);
-  o_pe = (lo + 1 < zn) ? CW_LDG(zw + lo + 1) : kOmega;
-}
-
 // ---- the walk ------------------------------------------------------------------------------------------------
 struct Walk {
   // zone
@@ -240,14 +216,22 @@ struct Walk {
     if (zn == 1) { pidx = 0; off = CW_LDG(zo); ps = kAlpha; pe = kOmega; }
   }
 
-  // (*Location).lookup(x).offset; moves the cached period to the one containing x.  The hit test is inline; the
-  // search lives out of line (it was inlined at ~20 sites: a third of every kernel's instructions).
+  // (*Location).lookup(x).offset; moves the cached period to the one containing x
   CW_HD int32_t lookup(int64_t x) {
     if (x >= ps && x < pe) return off;
-    int32_t n_idx, n_off;
-    int64_t n_ps, n_pe;
-    lookup_miss(zw, zo, zn, pidx, x >= pe, x, n_idx, n_off, n_ps, n_pe);
-    pidx = n_idx; off = n_off; ps = n_ps; pe = n_pe;
+    int32_t lo = 0, hi = zn;  // largest lo with when[lo] <= x  (when[0] == kAlpha)
+    if (pidx >= 0) {          // transitions are usually crossed one at a time: try the neighbours first
+      if (x >= pe) { lo = pidx + 1; if (lo + 1 >= zn || x < CW_LDG(zw + lo + 1)) hi = lo + 1; }
+      else { hi = pidx; if (hi - 1 >= 0 && x >= CW_LDG(zw + hi - 1)) lo = hi - 1; }
+    }
+    while (hi - lo > 1) {
+      const int32_t mid = (int32_t)((uint32_t)(lo + hi) >> 1);
+      if (x < CW_LDG(zw + mid)) hi = mid; else lo = mid;
+    }
+    pidx = lo;
+    off = CW_LDG(zo + lo);
+    ps = CW_LDG(zw + lo);
+    pe = (lo + 1 < zn) ? CW_LDG(zw + lo + 1) : kOmega;
     return off;
   }
 
