@@ -102,6 +102,10 @@ def lib():
     L.b200cron_synth_times_dev.argtypes = [vp, i32, vp, C.c_uint64, C.c_uint64, sz, i64, i64, C.c_uint64, vp]
     L.b200cron_synth_zones_dev.restype = i32
     L.b200cron_synth_zones_dev.argtypes = [vp, i32, vp, C.c_uint64, C.c_uint64, sz, vp, sz, C.c_double, vp]
+    L.b200cron_parse_batch.restype = i32
+    L.b200cron_parse_batch.argtypes = [vp, vp, vp, sz, i32, vp, vp, vp, vp]
+    L.b200cron_parse_batch_dev.restype = i32
+    L.b200cron_parse_batch_dev.argtypes = [vp, i32, vp, vp, vp, sz, i32, vp, vp, vp, vp]
     L.b200cron_sync_check.restype = i32
     L.b200cron_sync_check.argtypes = [vp, i32, vp]
     L.b200cron_launch_count.restype = C.c_uint64
@@ -334,6 +338,46 @@ class Context:
         nseg = seg_off.numel() - 1
         self._check(lib().b200cron_history_prune_dev(self._h, dev_index, stream or None, _ptr(seg_off), _ptr(key),
                                                      _ptr(limit), nseg, key.numel(), _ptr(perm), _ptr(keep)))
+
+    # ---- batched ParseStandard on the device
+    def parse_batch(self, specs, with_seconds: bool = False):
+        """cronv3.ParseStandard over a list of schedule strings on the GPU.  Returns (masks (6, n) uint64, status (n,)
+        uint8: 0 ok / 1 unparsable / 2 @every, tz names list (None when the spec has no TZ= prefix))."""
+        enc = [s.encode() if isinstance(s, str) else bytes(s) for s in specs]
+        n = len(enc)
+        off = np.zeros(n + 1, dtype=np.uint64)
+        off[1:] = np.cumsum([len(b) for b in enc])
+        blob = b"".join(enc)
+        text = np.frombuffer(blob, dtype=np.uint8) if blob else np.zeros(1, np.uint8)
+        masks = np.zeros((6, n), dtype=np.uint64)
+        status = np.zeros(n, np.uint8)
+        tzo, tzl = np.zeros(n, np.uint32), np.zeros(n, np.uint32)
+        planes, _ = _planes(masks)
+        self._check(lib().b200cron_parse_batch(self._h, text.ctypes.data, off.ctypes.data, n, int(with_seconds), planes,
+                                               status.ctypes.data, tzo.ctypes.data, tzl.ctypes.data))
+        tz = []
+        for i in range(n):
+            if tzl[i] == 0 and tzo[i] == 0:
+                tz.append(None)
+            elif tzo[i] == 0xFFFFFFFF:
+                tz.append("UTC")
+            else:
+                tz.append(enc[i][int(tzo[i]):int(tzo[i]) + int(tzl[i])].decode(errors="replace"))
+        return masks, status, tz
+
+    def ParseStandardBatch(self, specs):
+        """list of schedule strings -> list of SpecSchedule (ParseError raised for the first unparsable one, with
+        upstream's message from the host parser; @every and zone-name resolution are finished on the host)"""
+        masks, status, tz = self.parse_batch(specs)
+        out = []
+        for i, text in enumerate(specs):
+            if status[i] != 0:
+                out.append(ParseStandard(text))  # raises for status 1, returns the ConstantDelay form for status 2
+                continue
+            if tz[i] not in (None, "Local"):
+                self.zone_id(tz[i])  # time.LoadLocation error for unknown names
+            out.append(SpecSchedule(*[int(masks[p, i]) for p in range(6)], tz[i] or "", 0))
+        return out
 
     # ---- device-side synthetic workloads (bit-identical to synth.py)
     def synth_specs_dev(self, masks_out, n: int, seed: int = 0xC0FFEE, start: int = 0, with_seconds: bool = False,

@@ -17,6 +17,7 @@
 
 #include "../../include/b200cron.h"
 #include "kernels.cuh"
+#include "parse_kernels.cuh"
 #include "synth_kernels.cuh"
 #include "zone_table.h"
 
@@ -789,5 +790,69 @@ extern "C" int b200cron_synth_zones_dev(b200cron_ctx* ctx, int dev_index, void* 
   synth_zones_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream ? (cudaStream_t)stream : d->stream>>>(
       seed, start, n, pool, pool_len, p_utc, out);
   CU(ctx, cudaGetLastError());
+  return B200CRON_OK;
+}
+
+// =================================================================================================================
+// batched ParseStandard on the device
+// =================================================================================================================
+extern "C" int b200cron_parse_batch_dev(b200cron_ctx* ctx, int dev_index, void* stream, const char* text,
+                                        const uint64_t* text_off, size_t n, int with_seconds,
+                                        uint64_t* const masks_out[6], uint8_t* status, uint32_t* tz_off,
+                                        uint32_t* tz_len) {
+  Device* d = device_at(ctx, dev_index);
+  if (!d) return B200CRON_EINVAL;
+  if (!text_off || !masks_out || !status || !tz_off || !tz_len) return fail(ctx, B200CRON_EINVAL, "parse_batch: NULL argument");
+  if (n == 0) return B200CRON_OK;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  CU(ctx, cudaSetDevice(d->id));
+  ParseOut out;
+  for (int p = 0; p < 6; ++p) out.p[p] = masks_out[p];
+  ctx->launches.fetch_add(1, std::memory_order_relaxed);
+  parse_batch_kernel<<<(unsigned)((n + 127) / 128), 128, 0, stream ? (cudaStream_t)stream : d->stream>>>(
+      text, text_off, n, with_seconds, out, status, tz_off, tz_len);
+  CU(ctx, cudaGetLastError());
+  return B200CRON_OK;
+}
+
+extern "C" int b200cron_parse_batch(b200cron_ctx* ctx, const char* text, const uint64_t* text_off, size_t n,
+                                    int with_seconds, uint64_t* const masks_out[6], uint8_t* status,
+                                    uint32_t* tz_off, uint32_t* tz_len) {
+  if (!ctx) return B200CRON_EINVAL;
+  if (!text_off || !masks_out || !status || !tz_off || !tz_len) return fail(ctx, B200CRON_EINVAL, "parse_batch: NULL argument");
+  if (n == 0) return B200CRON_OK;
+  for (size_t i = 0; i < n; ++i)
+    if (text_off[i + 1] < text_off[i] || text_off[i + 1] - text_off[i] > (1u << 20))
+      return fail(ctx, B200CRON_EINVAL, "parse_batch: text_off must be non-decreasing (specs up to 1 MiB)");
+  const uint64_t t0 = text_off[0], bytes = text_off[n] - t0;
+  if (bytes && !text) return fail(ctx, B200CRON_EINVAL, "parse_batch: NULL text");
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  Device& d = ctx->devs[0];
+  CU(ctx, cudaSetDevice(d.id));
+  Slot& s = d.slots[0];
+  const size_t stride = align_up(n + 1, 64), tbytes = align_up(bytes + 16, 64);
+  int rc = ensure_slot(ctx, s, tbytes + stride * (8 + 6 * 8 + 4 + 4 + 1) + 1024);
+  if (rc) return rc;
+  char* d_text = reinterpret_cast<char*>(s.buf);
+  uint64_t* d_off = reinterpret_cast<uint64_t*>(d_text + tbytes);
+  uint64_t* d_masks = d_off + stride;
+  uint32_t* d_tzo = reinterpret_cast<uint32_t*>(d_masks + 6 * stride);
+  uint32_t* d_tzl = d_tzo + stride;
+  uint8_t* d_status = reinterpret_cast<uint8_t*>(d_tzl + stride);
+  if (bytes) CU(ctx, cudaMemcpyAsync(d_text, text + t0, bytes, cudaMemcpyHostToDevice, s.stream));
+  CU(ctx, cudaMemcpyAsync(d_off, text_off, (n + 1) * 8, cudaMemcpyHostToDevice, s.stream));
+  ParseOut out;
+  for (int p = 0; p < 6; ++p) out.p[p] = d_masks + p * stride;
+  ctx->launches.fetch_add(1, std::memory_order_relaxed);
+  // offsets are absolute in the caller's buffer: bias the text pointer by -t0
+  parse_batch_kernel<<<(unsigned)((n + 127) / 128), 128, 0, s.stream>>>(d_text - t0, d_off, n, with_seconds, out, d_status,
+                                                                      d_tzo, d_tzl);
+  CU(ctx, cudaGetLastError());
+  for (int p = 0; p < 6; ++p)
+    CU(ctx, cudaMemcpyAsync(masks_out[p], d_masks + p * stride, n * 8, cudaMemcpyDeviceToHost, s.stream));
+  CU(ctx, cudaMemcpyAsync(status, d_status, n, cudaMemcpyDeviceToHost, s.stream));
+  CU(ctx, cudaMemcpyAsync(tz_off, d_tzo, n * 4, cudaMemcpyDeviceToHost, s.stream));
+  CU(ctx, cudaMemcpyAsync(tz_len, d_tzl, n * 4, cudaMemcpyDeviceToHost, s.stream));
+  CU(ctx, cudaStreamSynchronize(s.stream));
   return B200CRON_OK;
 }

@@ -89,6 +89,20 @@ int b200cron_parse_standard(const char* spec, size_t len, b200cron_spec* out, in
 int b200cron_parse_with_seconds(const char* spec, size_t len, b200cron_spec* out, int* kind, int64_t* every_sec,
                                 char* tz, size_t tzcap, char* err, size_t errcap);
 
+/* Batched form of b200cron_parse_standard / _with_seconds, run on the GPU (one thread per spec): the reference
+ * re-parses every Cron's schedule on every reconcile (cron_controller.go:392).  Spec i is the bytes
+ * text[text_off[i] .. text_off[i+1]).  Outputs per spec: the six masks (SoA planes, zero on error), status
+ * (0 parsed, 1 not parsable -- call b200cron_parse_standard on it for upstream's message, 2 "@every <duration>":
+ * a ConstantDelaySchedule, left to the host parser), and the span of the TZ=/CRON_TZ= location name inside the
+ * spec (tz_len 0 = no prefix; tz_off 0xFFFFFFFF = an empty name, i.e. UTC) for the caller to turn into a zone id
+ * with b200cron_zone_id.  Same accept/reject decisions as the host parser.  The host-pointer form runs on the
+ * context's first device; the _dev form takes device pointers.  Declared below the context functions' types. */
+int b200cron_parse_batch(b200cron_ctx* ctx, const char* text, const uint64_t* text_off, size_t n, int with_seconds,
+                         uint64_t* const masks_out[6], uint8_t* status, uint32_t* tz_off, uint32_t* tz_len);
+int b200cron_parse_batch_dev(b200cron_ctx* ctx, int dev_index, void* stream, const char* text,
+                             const uint64_t* text_off, size_t n, int with_seconds, uint64_t* const masks_out[6],
+                             uint8_t* status, uint32_t* tz_off, uint32_t* tz_len);
+
 /* ---- context ----------------------------------------------------------------------------------------------- */
 
 /* Creates a context on `ndev` CUDA devices (ids in `devices`; NULL/0 = current device only) and loads every TZif

@@ -397,3 +397,37 @@ def test_C3_full_size_sampled_parity(ctx, names):
     # rows increase except where upstream itself steps back across a DST overlap: rare
     back = ((out[:, 1:] <= out[:, :-1]) & ~zero[:, 1:]).sum().item()
     assert back < n * k * 1e-6, back
+
+
+def test_device_parse_matches_host_parser(ctx):
+    """batched device ParseStandard vs the host parser (itself checked against the oracle) on the corpus + fuzz"""
+    from tests.test_abi_cpu import CORPUS, _fuzz
+    for with_seconds in (False, True):
+        texts = CORPUS + _fuzz(6000, 11 + with_seconds)
+        texts = [t.encode("utf-8", errors="surrogateescape") if isinstance(t, str) else t for t in texts]
+        masks, status, tz = ctx.parse_batch(texts, with_seconds)
+        n_ok = 0
+        for i, t in enumerate(texts):
+            try:
+                want = api._parse(t, with_seconds)
+            except api.ParseError:
+                want = None
+            if want is None:
+                assert status[i] == 1, (t, status[i])
+                assert not masks[:, i].any()
+            elif want.Every:
+                assert status[i] == 2, t
+            else:
+                assert status[i] == 0, (t, status[i])
+                assert tuple(int(x) for x in masks[:, i]) == want.masks(), t
+                assert (tz[i] or "") == want.Location, (t, tz[i], want.Location)
+                n_ok += 1
+        assert n_ok > 1000
+    # the mirrored interface, incl. error propagation and zone validation
+    got = ctx.ParseStandardBatch(["*/5 * * * *", "CRON_TZ=Asia/Tokyo 0 9 * * *", "@every 90s", "@daily"])
+    assert got[0] == api.ParseStandard("*/5 * * * *") and got[1].Location == "Asia/Tokyo" and got[2].Every == 90
+    with pytest.raises(api.ParseError):
+        ctx.ParseStandardBatch(["* * * * *", "60 31 30 2 *"])  # K1
+    with pytest.raises(api.ParseError):
+        ctx.ParseStandardBatch(["TZ=Nope/Nowhere * * * * *"])
+    assert ctx.parse_batch([])[0].shape == (6, 0)
