@@ -412,6 +412,9 @@ def test_device_parse_matches_host_parser(ctx):
                 want = api._parse(t, with_seconds)
             except api.ParseError:
                 want = None
+            if status[i] == 2:  # "@every ..." is always handed to the host parser, which validates the duration
+                assert b"@every " in t and (want is None or want.Every), t
+                continue
             if want is None:
                 assert status[i] == 1, (t, status[i])
                 assert not masks[:, i].any()
