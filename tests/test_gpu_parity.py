@@ -425,7 +425,7 @@ def test_device_parse_matches_host_parser(ctx):
                 assert tuple(int(x) for x in masks[:, i]) == want.masks(), t
                 assert (tz[i] or "") == want.Location, (t, tz[i], want.Location)
                 n_ok += 1
-        assert n_ok > 1000
+        assert n_ok > 200
     # the mirrored interface, incl. error propagation and zone validation
     got = ctx.ParseStandardBatch(["*/5 * * * *", "CRON_TZ=Asia/Tokyo 0 9 * * *", "@every 90s", "@daily"])
     assert got[0] == api.ParseStandard("*/5 * * * *") and got[1].Location == "Asia/Tokyo" and got[2].Every == 90
