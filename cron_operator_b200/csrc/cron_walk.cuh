@@ -204,15 +204,19 @@ struct Walk {
   int32_t sod;  // local second of day
   int32_t Y, M, D;
   bool today_ok;  // the resident day is known to satisfy the month and day masks (set when a fire was found on it)
+  // chained calls (NextN): day mask of the resident month, and the day's last matching second (86400 = not set)
+  uint32_t dm_month;
+  bool dm_ok;
+  int32_t tod_last;
 
   CW_HD void bind_utc() {
-    zw = nullptr; zo = nullptr; zf = nullptr; zn = 1; pidx = 0; off = 0; ps = kAlpha; pe = kOmega; today_ok = false;
+    zw = nullptr; zo = nullptr; zf = nullptr; zn = 1; pidx = 0; off = 0; ps = kAlpha; pe = kOmega; today_ok = false; dm_ok = false; dm_month = 0; tod_last = 86400;
   }
   CW_HD void bind_zone(const ZoneTable& zt, int32_t zone) {
     const int32_t a = CW_LDG(zt.zstart + zone), b = CW_LDG(zt.zstart + zone + 1);
     zw = zt.when + a; zo = zt.off + a; zf = zt.fpre + a; zn = b - a;
     pidx = -1; off = 0; ps = 1; pe = 0;  // empty cache
-    today_ok = false;
+    today_ok = false; dm_ok = false; dm_month = 0; tod_last = 86400;
     if (zn == 1) { pidx = 0; off = CW_LDG(zo); ps = kAlpha; pe = kOmega; }
   }
 
@@ -253,6 +257,7 @@ struct Walk {
     sod = r * 128 + (int32_t)(l & 127);
     civil_from_days(dn, Y, M, D);
     today_ok = false;
+    dm_ok = false;
   }
 
   // time.Date(y, mo, d, h, mi, s, 0, loc): as-if-UTC seconds, then the two-lookup offset resolution
@@ -295,6 +300,7 @@ struct Walk {
   // move the resident fields forward by k whole days inside the same period (k >= 1, small)
   CW_HD void advance_days(int32_t k) {
     today_ok = false;
+    dm_ok = false;
     dn += k;
     D += k;
     int32_t dim = days_in_month(Y, M);
@@ -490,6 +496,11 @@ CW_HD int64_t walk_next(const Spec& s, Walk& w) {
 }
 
 
+// last matching second of a day (for chained calls: past it, the day has no fire left)
+CW_HD int32_t spec_tod_last(const Spec& s) {
+  return (31 - clz32(s.hour)) * 3600 + (63 - clz64(s.minute)) * 60 + (63 - clz64(s.second));
+}
+
 // first matching time of day >= sod on the same day, or -1.  Branch-free: the three candidates (same minute, later
 // minute of the same hour, later hour) are all computed and the earliest valid one is selected.
 CW_HD int32_t next_tod_ge(const Spec& s, int32_t sod) {
@@ -584,24 +595,32 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
     today = (dm >> w.D) & 1u;  // == month matches && dayMatches(t)
   }
   if (today) {
-    int64_t r;
-    int32_t rsod;
-    if (find_tod_today(s, w, w.t, sod, &r, &rsod)) {
-      w.t = r;
-      w.sod = rsod;
-      w.today_ok = true;
-      *out = r;
-      return true;
+    if (sod <= w.tod_last) {  // (chained calls know the day's last fire: past it there is nothing to search)
+      int64_t r;
+      int32_t rsod;
+      if (find_tod_today(s, w, w.t, sod, &r, &rsod)) {
+        w.t = r;
+        w.sod = rsod;
+        w.today_ok = true;
+        if (have_dm) { w.dm_month = dm; w.dm_ok = true; }
+        *out = r;
+        return true;
+      }
     }
     if (w.t + (86400 - sod) >= w.pe) return false;  // the Hour()==0 wrap must happen inside this period
   }
   if (!have_dm) {
     leap = is_leap(w.Y);
-    const int32_t dim = (w.M == 2) ? (leap ? 29 : 28) : 30 + (int32_t)((0x15AAu >> w.M) & 1u);
-    const uint32_t valid = (uint32_t)((2ULL << dim) - 2ULL);
-    const uint32_t dowm = (uint32_t)((rep >> weekday_of(first_dn)) << 1);
-    dm = month_ok ? ((s.star ? (s.dom & dowm) : (s.dom | dowm)) & valid) : 0u;
+    if (w.dm_ok) {
+      dm = w.dm_month;  // cached by the call that brought the walk into this month
+    } else {
+      const int32_t dim = (w.M == 2) ? (leap ? 29 : 28) : 30 + (int32_t)((0x15AAu >> w.M) & 1u);
+      const uint32_t valid = (uint32_t)((2ULL << dim) - 2ULL);
+      const uint32_t dowm = (uint32_t)((rep >> weekday_of(first_dn)) << 1);
+      dm = month_ok ? ((s.star ? (s.dom & dowm) : (s.dom | dowm)) & valid) : 0u;
+    }
   }
+  const uint32_t dm_cur = dm;  // full mask of the resident month
 
   // ---- calendar search for the next matching day after today, visiting matching months only ----
   const int32_t year_limit = w.Y + 5;
@@ -629,6 +648,8 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
     dm = (s.star ? (s.dom & dowm) : (s.dom | dowm)) & valid;
   }
   const bool found = dm != 0;
+  // day mask of the month the result lands in (full mask when the loop advanced, else the resident month's)
+  const uint32_t dm_found = (Yc == w.Y && Mc == w.M) ? dm_cur : dm;
   const int32_t Dc = found ? ctz32(dm) : 1;
   const int32_t found_dn = found ? first_dn + Dc - 1 : jan1;  // not found: Jan 1 of year_limit + 1 (the WRAP that fails)
   const int64_t x_mid = (int64_t)found_dn * 86400;            // local midnight of the fire day
@@ -637,6 +658,7 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
     w.t = x_mid + s.tod1 - w.off;
     w.dn = found_dn; w.sod = s.tod1; w.Y = Yc; w.M = Mc; w.D = Dc;
     w.today_ok = true;
+    w.dm_month = dm_found; w.dm_ok = true;
     *out = w.t;
     return true;
   }
@@ -670,6 +692,7 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
   w.t = r;
   w.dn = found_dn; w.sod = rsod; w.Y = Yc; w.M = Mc; w.D = Dc;
   w.today_ok = true;
+  w.dm_month = dm_found; w.dm_ok = true;
   *out = r;
   return true;
 }
@@ -707,6 +730,7 @@ SlowResult walk_next_outlined(Spec s, Walk w) {
   x.w.lookup(x.w.t);  // fast_next may have moved the period cache; the step emulation wants it on t
   x.r = walk_next(s, x.w);
   x.w.today_ok = false;  // the emulation can end on a day upstream never re-checked
+  x.w.dm_ok = false;
   return x;
 }
 // kOutline = true: call the single out-of-line copy (unmet / list kernels: several phases share it and the kernel
@@ -722,6 +746,7 @@ CW_HD int64_t next_slow(const Spec& s, Walk& w) {
   w.lookup(w.t);
   const int64_t r = walk_next(s, w);
   w.today_ok = false;
+  w.dm_ok = false;
   return r;
 }
 template <bool kOutline>

@@ -106,6 +106,7 @@ next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* 
     Walk w;
     int64_t t = e ? fr[1] : fr[0];
     bool ok = bind_checked(w, zt, e ? zz[1] : zz[0], t, err);
+    if (KT != 1 && !ss.never) w.tod_last = cronwalk::spec_tod_last(ss);  // lets chained calls skip exhausted days
     const int row = 2 * lane + e;
 #pragma unroll 1
     for (int j = 0; j < kk; ++j) {

@@ -56,6 +56,7 @@ void shim_next_n(void* table, const uint64_t* const masks[6], const int32_t* zon
     Walk w;
     const int32_t z = zone_id ? zone_id[i] : 0;
     if (z == 0) w.bind_utc(); else w.bind_zone(zt, z);
+    if (k != 1 && !s.never) w.tod_last = spec_tod_last(s);  // as next_n_kernel does
     int64_t t = from[i];
     bool resident = false;
     for (int q = 0; q < k; ++q) {
