@@ -573,10 +573,11 @@ CW_HD bool find_tod_today(const Spec& s, Walk& w, int64_t t, int32_t sod, int64_
 CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
   const int32_t sod = w.sod;
   const bool zoned = w.zn > 1;
-  if (zoned) {
-    if (w.off % 60 != 0) return false;
-    if (!w.natural((int64_t)w.dn * 86400 + (sod / 3600) * 3600)) return false;  // hour reset Date(Y,M,D,h,0,0)
-  }
+  // Zoned prerequisites, evaluated without an early exit inside the zoned branch: with a `return` in there the
+  // compiler kept UTC and zoned lanes apart for the rest of the function (every mixed warp ran it twice).
+  // natural() is trivially true for UTC (one infinite period, offset 0), so all lanes run the same code.
+  const bool prereq = (w.off % 60 == 0) && w.natural((int64_t)w.dn * 86400 + (sod / 3600) * 3600);  // hour reset Date(Y,M,D,h,0,0)
+  if (!prereq) return false;
   const bool month_ok = (s.month >> w.M) & 1u;
   const uint64_t rep = (uint64_t)s.dow * 0x0000000810204081ULL;  // dow pattern repeated every 7 bits
   bool leap = false;

@@ -101,15 +101,19 @@ next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* 
   int64_t ra = kZero, rb = kZero;
 #pragma unroll 1
   for (int e = 0; e < 2; ++e) {
-    if (i0 + e >= n) break;
+    const bool live = i0 + e < n;  // out-of-range lanes stay in the loops (doing nothing) so the warp can re-sync
     const Spec ss = e ? sp[1] : sp[0];
     Walk w;
     int64_t t = e ? fr[1] : fr[0];
-    bool ok = bind_checked(w, zt, e ? zz[1] : zz[0], t, err);
+    bool ok = live && bind_checked(w, zt, e ? zz[1] : zz[0], t, err);
+    if (!live) w.bind_utc();
     if (KT != 1 && !ss.never) w.tod_last = cronwalk::spec_tod_last(ss);  // lets chained calls skip exhausted days
     const int row = 2 * lane + e;
 #pragma unroll 1
     for (int j = 0; j < kk; ++j) {
+      // Every lane runs exactly kk iterations: re-converge here, otherwise lanes that took the short path of one
+      // iteration run ahead and the warp executes each path of each iteration separately.
+      __syncwarp();
       if (ok && t != kZero) {
         t = cronwalk::next_from(ss, w, t, j > 0);
         // chained calls keep walking: re-check the zoned horizon (UTC never trips it)
