@@ -578,6 +578,27 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
   // natural() is trivially true for UTC (one infinite period, offset 0), so all lanes run the same code.
   const bool prereq = (w.off % 60 == 0) && w.natural((int64_t)w.dn * 86400 + (sod / 3600) * 3600);  // hour reset Date(Y,M,D,h,0,0)
   if (!prereq) return false;
+  // Chained-call shortcut: the previous fire was the last of its (matching) day, the resident month's day mask is
+  // cached, and the next matching day lies in the same month.  Upstream wraps at the next local midnight
+  // (Add-based, must happen inside this period), crosses the non-matching days with AddDate steps at hour 0 (all
+  // those midnights natural in this period: the range is convex, so the first and the last suffice) and runs the
+  // Add-based loops from the fire day's midnight to its first fire (inside this period).  Anything else falls
+  // through to the general code below.
+  if (w.today_ok && w.dm_ok && sod > w.tod_last) {
+    const uint32_t rest = w.dm_month & ~((2u << w.D) - 1u);
+    if (rest) {
+      const int32_t Dn = ctz32(rest);
+      const int32_t k = Dn - w.D;
+      const int64_t x1 = (int64_t)(w.dn + 1) * 86400, xk = (int64_t)(w.dn + k) * 86400;
+      const int64_t r = xk - w.off + s.tod1;
+      if (w.t + (86400 - sod) < w.pe && w.natural(x1) && w.natural(xk) && r < w.pe) {
+        w.t = r;
+        w.dn += k; w.D = Dn; w.sod = s.tod1;
+        *out = r;
+        return true;
+      }
+    }
+  }
   const bool month_ok = (s.month >> w.M) & 1u;
   const uint64_t rep = (uint64_t)s.dow * 0x0000000810204081ULL;  // dow pattern repeated every 7 bits
   bool leap = false;
