@@ -121,8 +121,9 @@ cudaError_t launch_next(b200cron_ctx* ctx, const Device& d, cudaStream_t st, con
   const size_t smem = k == 1 ? 0 : (size_t)kNextTile * k * sizeof(int64_t);
   ctx->launches.fetch_add(1, std::memory_order_relaxed);
   if (k == 1 && !getenv("B200CRON_NEXT1_PAIRED")) {  // one spec per lane (finer waves); the env var selects the paired kernel
-    next1_kernel<<<(unsigned)((n + kNext1Threads - 1) / kNext1Threads), kNext1Threads, 0, st>>>(m, zone, from, n, out,
-                                                                                               d.zt, d.d_err);
+    const unsigned g1 = (unsigned)((n + kNext1Threads - 1) / kNext1Threads);
+    if (zone) next1_kernel<false><<<g1, kNext1Threads, 0, st>>>(m, zone, from, n, out, d.zt, d.d_err);
+    else next1_kernel<true><<<g1, kNext1Threads, 0, st>>>(m, zone, from, n, out, d.zt, d.d_err);  // all-UTC launch
     return cudaGetLastError();
   }
   switch (k) {

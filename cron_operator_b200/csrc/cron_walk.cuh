@@ -570,13 +570,15 @@ CW_HD bool find_tod_today(const Spec& s, Walk& w, int64_t t, int32_t sod, int64_
 //
 // The code is straight-line on purpose (one lane per spec, 32 specs per warp): the only data-dependent control flow
 // is the trip count of the month loop, which visits matching months only.
+// kUtcOnly: the launch has no zone ids at all (every spec in UTC): the zone logic compiles away.
+template <bool kUtcOnly = false>
 CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
   const int32_t sod = w.sod;
-  const bool zoned = w.zn > 1;
+  const bool zoned = !kUtcOnly && w.zn > 1;
   // Zoned prerequisites, evaluated without an early exit inside the zoned branch: with a `return` in there the
   // compiler kept UTC and zoned lanes apart for the rest of the function (every mixed warp ran it twice).
   // natural() is trivially true for UTC (one infinite period, offset 0), so all lanes run the same code.
-  const bool prereq = (w.off % 60 == 0) && w.natural((int64_t)w.dn * 86400 + (sod / 3600) * 3600);  // hour reset Date(Y,M,D,h,0,0)
+  const bool prereq = kUtcOnly || ((w.off % 60 == 0) && w.natural((int64_t)w.dn * 86400 + (sod / 3600) * 3600));  // hour reset Date(Y,M,D,h,0,0)
   if (!prereq) return false;
   // Chained-call shortcut: the previous fire was the last of its (matching) day, the resident month's day mask is
   // cached, and the next matching day lies in the same month.  Upstream wraps at the next local midnight
@@ -722,6 +724,7 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
 // Next(t) in two halves so that kernels can run the straight-line half for several specs in lock step and share one
 // copy of the step emulation: next_try() = t.Add(1s), field decomposition and the closed form; it returns false when
 // only walk_next() can decide (then call next_slow()).  `resident` = w already holds the fields of `t`.
+template <bool kUtcOnly = false>
 CW_HD bool next_try(const Spec& s, Walk& w, int64_t t, bool resident, int64_t* out) {
   CW_COUNT(next);
   if (s.never) { *out = kZero; return true; }
@@ -732,7 +735,7 @@ CW_HD bool next_try(const Spec& s, Walk& w, int64_t t, bool resident, int64_t* o
   } else {
     w.load(t1);
   }
-  return fast_next(s, w, out);
+  return fast_next<kUtcOnly>(s, w, out);
 }
 // The step emulation is rare and large (thousands of instructions).  On the device it lives out of line, once per
 // kernel image, and takes/returns its state by value so that callers keep their Walk in registers on the fast path
@@ -771,10 +774,10 @@ CW_HD int64_t next_slow(const Spec& s, Walk& w) {
   w.dm_ok = false;
   return r;
 }
-template <bool kOutline>
+template <bool kOutline, bool kUtcOnly = false>
 CW_HD int64_t next_from_t(const Spec& s, Walk& w, int64_t t, bool resident) {
   int64_t r;
-  if (next_try(s, w, t, resident, &r)) return r;
+  if (next_try<kUtcOnly>(s, w, t, resident, &r)) return r;
   return next_slow<kOutline>(s, w);
 }
 CW_HD int64_t next_from(const Spec& s, Walk& w, int64_t t, bool resident) { return next_from_t<false>(s, w, t, resident); }

@@ -168,6 +168,7 @@ next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* 
 #endif
 constexpr int kNext1Threads = B200CRON_NEXT1_THREADS;
 
+template <bool kUtcOnly>
 __global__ void __launch_bounds__(kNext1Threads, B200CRON_NEXT1_MINBLOCKS)
 next1_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* __restrict__ from, size_t n,
              int64_t* __restrict__ out, ZoneTable zt, int* __restrict__ err) {
@@ -179,7 +180,7 @@ next1_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* _
   const int32_t zone = zone_id ? __ldg(zone_id + i) : 0;
   Walk w;
   const bool ok = bind_checked(w, zt, zone, t, err);
-  out[i] = ok ? cronwalk::next_from(s, w, t, false) : kZero;
+  out[i] = ok ? cronwalk::next_from_t<false, kUtcOnly>(s, w, t, false) : kZero;
 }
 
 // -------------------------------------------------------------------------------------------------------------
