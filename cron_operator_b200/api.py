@@ -171,15 +171,22 @@ def _ptr(a):
     return a.data_ptr()  # torch tensor
 
 
-def _planes(masks):
+def _planes(masks, five_field: bool = False):
+    """six plane pointers; five_field=True passes NULL for the seconds plane (ParseStandard schedules fire at second 0)"""
     if isinstance(masks, np.ndarray):
         assert masks.dtype == np.uint64 and masks.ndim == 2 and masks.shape[0] == 6 and masks.flags.c_contiguous
-        return (C.c_void_p * 6)(*[masks[i].ctypes.data for i in range(6)]), masks.shape[1]
+        ptrs = [masks[i].ctypes.data for i in range(6)]
+        if five_field:
+            ptrs[0] = None
+        return (C.c_void_p * 6)(*ptrs), masks.shape[1]
     # torch tensor (6, n) int64/uint64 on the device, or a sequence of 6 tensors
     planes = [masks[i] for i in range(6)]
     for p in planes:
         assert p.is_contiguous() and p.element_size() == 8
-    return (C.c_void_p * 6)(*[p.data_ptr() for p in planes]), planes[0].numel()
+    ptrs = [p.data_ptr() for p in planes]
+    if five_field:
+        ptrs[0] = None
+    return (C.c_void_p * 6)(*ptrs), planes[0].numel()
 
 
 class Context:
@@ -249,8 +256,8 @@ class Context:
         return int(lib().b200cron_launch_count(self._h))
 
     # ---- host-pointer calls (numpy in, numpy out; copies inside the library)
-    def next_n(self, masks: np.ndarray, from_, k: int = 1, zone_id=None, out=None) -> np.ndarray:
-        planes, n = _planes(masks)
+    def next_n(self, masks: np.ndarray, from_, k: int = 1, zone_id=None, out=None, five_field: bool = False) -> np.ndarray:
+        planes, n = _planes(masks, five_field)
         from_ = np.ascontiguousarray(from_, dtype=np.int64)
         zid = None if zone_id is None else np.ascontiguousarray(zone_id, dtype=np.int32)
         if out is None:
@@ -320,8 +327,9 @@ class Context:
         return perm, keep
 
     # ---- device-pointer calls (torch tensors resident on device `dev_index`; enqueue only)
-    def next_n_dev(self, masks, from_, out, k: int = 1, zone_id=None, dev_index: int = 0, stream: int = 0):
-        planes, n = _planes(masks)
+    def next_n_dev(self, masks, from_, out, k: int = 1, zone_id=None, dev_index: int = 0, stream: int = 0,
+                   five_field: bool = False):
+        planes, n = _planes(masks, five_field)
         self._check(lib().b200cron_next_n_dev(self._h, dev_index, stream or None, planes, _ptr(zone_id), _ptr(from_),
                                               n, k, _ptr(out)))
 

@@ -93,6 +93,12 @@ int ensure_slot(b200cron_ctx* ctx, Slot& s, size_t bytes) {
   return 0;
 }
 
+bool is_pinned_host(const void* p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return a.type == cudaMemoryTypeHost;
+}
+
 bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 // ---- launches -------------------------------------------------------------------------------------------------
@@ -116,7 +122,7 @@ cudaError_t launch_next(b200cron_ctx* ctx, const Device& d, cudaStream_t st, con
                         const int64_t* from, size_t n, int k, int64_t* out) {
   if (n == 0) return cudaSuccess;
   bool vec = aligned16(from) && aligned16(out) && (!zone || (reinterpret_cast<uintptr_t>(zone) & 7u) == 0);
-  for (int p = 0; p < 6; ++p) vec = vec && aligned16(m.p[p]);
+  for (int p = 0; p < 6; ++p) vec = vec && (m.p[p] == nullptr || aligned16(m.p[p]));
   const unsigned grid = (unsigned)((n + kNextTile - 1) / kNextTile);
   const size_t smem = k == 1 ? 0 : (size_t)kNextTile * k * sizeof(int64_t);
   ctx->launches.fetch_add(1, std::memory_order_relaxed);
@@ -355,8 +361,34 @@ extern "C" int b200cron_next_n(b200cron_ctx* ctx, const uint64_t* const masks[6]
                                const int64_t* from, size_t n, int k, int64_t* out) {
   if (!ctx) return B200CRON_EINVAL;
   if (!masks || !from || !out || k < 1 || k > 64) return fail(ctx, B200CRON_EINVAL, "next_n: bad argument (1 <= k <= 64)");
+  for (int p = 1; p < 6; ++p)
+    if (!masks[p]) return fail(ctx, B200CRON_EINVAL, "next_n: only the seconds plane (masks[0]) may be NULL");
   std::lock_guard<std::mutex> lk(ctx->mu);
   const int G = (int)ctx->devs.size();
+  // Zero-copy path: when every buffer is pinned host memory (b200cron_host_alloc / cudaHostAlloc / cudaHostRegister)
+  // the kernels read and write it in place over PCIe -- no staging copies, the transfer overlaps the walk by itself.
+  {
+    bool pinned = is_pinned_host(from) && is_pinned_host(out) && (!zone_id || is_pinned_host(zone_id));
+    for (int p = 0; p < 6 && pinned; ++p) pinned = (p == 0 && !masks[0]) || is_pinned_host(masks[p]);
+    if (pinned && n > 0) {
+      for (int g = 0; g < G; ++g) {
+        Device& d = ctx->devs[g];
+        const Shard sh = shard_of(n, g, G);
+        if (sh.hi <= sh.lo) continue;
+        CU(ctx, cudaSetDevice(d.id));
+        MaskPlanes m;
+        for (int p = 0; p < 6; ++p) m.p[p] = masks[p] ? masks[p] + sh.lo : nullptr;
+        CU(ctx, launch_next(ctx, d, d.stream, m, zone_id ? zone_id + sh.lo : nullptr, from + sh.lo, sh.hi - sh.lo, k,
+                            out + sh.lo * (size_t)k));
+        CU(ctx, collect_err(d, d.stream));
+      }
+      for (Device& d : ctx->devs) {
+        CU(ctx, cudaSetDevice(d.id));
+        CU(ctx, cudaStreamSynchronize(d.stream));
+      }
+      return check_err_flags(ctx);
+    }
+  }
   // per-chunk staging layout: 6 mask planes | from | out (k per spec) | zone ids
   const size_t per_spec = 6 * 8 + 8 + (size_t)k * 8 + 4;
   for (int g = 0; g < G; ++g) {
@@ -381,6 +413,7 @@ extern "C" int b200cron_next_n(b200cron_ctx* ctx, const uint64_t* const masks[6]
       int32_t* d_zone = reinterpret_cast<int32_t*>(d_out + stride * k);
       MaskPlanes m;
       for (int p = 0; p < 6; ++p) {
+        if (!masks[p]) { m.p[p] = nullptr; continue; }  // only plane 0 may be NULL (checked above)
         m.p[p] = d_masks + p * stride;
         CU(ctx, cudaMemcpyAsync(d_masks + p * stride, masks[p] + c, cn * 8, cudaMemcpyHostToDevice, s.stream));
       }

@@ -71,6 +71,7 @@ next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* 
   if (kVec && full) {
 #pragma unroll
     for (int p = 0; p < 6; ++p) {
+      if (p == 0 && m.p[0] == nullptr) { mk[0][0] = 1; mk[0][1] = 1; continue; }  // 5-field schedules: second 0
       const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2*>(m.p[p] + i0));
       mk[p][0] = v.x; mk[p][1] = v.y;
     }
@@ -84,7 +85,8 @@ next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* 
 #pragma unroll
     for (int e = 0; e < 2; ++e) {
 #pragma unroll
-      for (int p = 0; p < 6; ++p) mk[p][e] = (i0 + e < n) ? __ldg(m.p[p] + i0 + e) : 0;
+      for (int p = 0; p < 6; ++p)
+        mk[p][e] = (i0 + e < n) ? ((p == 0 && m.p[0] == nullptr) ? 1ULL : __ldg(m.p[p] + i0 + e)) : 0;
       if (i0 + e < n) {
         fr[e] = __ldg(from + i0 + e);
         if (zone_id) zz[e] = __ldg(zone_id + i0 + e);
@@ -174,7 +176,7 @@ next1_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* _
              int64_t* __restrict__ out, ZoneTable zt, int* __restrict__ err) {
   const size_t i = (size_t)blockIdx.x * kNext1Threads + threadIdx.x;
   if (i >= n) return;
-  const Spec s = cronwalk::make_spec(__ldg(m.p[0] + i), __ldg(m.p[1] + i), __ldg(m.p[2] + i), __ldg(m.p[3] + i),
+  const Spec s = cronwalk::make_spec(m.p[0] ? __ldg(m.p[0] + i) : 1ULL, __ldg(m.p[1] + i), __ldg(m.p[2] + i), __ldg(m.p[3] + i),
                                      __ldg(m.p[4] + i), __ldg(m.p[5] + i));
   const int64_t t = __ldg(from + i);
   const int32_t zone = zone_id ? __ldg(zone_id + i) : 0;

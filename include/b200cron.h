@@ -129,7 +129,9 @@ void b200cron_host_free(void* p);
 /* Replaces (*SpecSchedule).Next [robfig/cron v3.0.1 spec.go] as called at cron_controller.go:405,409,436, batched:
  * out[i*k + j] = the (j+1)-th fire time after from[i] (each the Next() of the previous one), or
  * B200CRON_ZERO_TIME from the first call that finds no fire time within upstream's 5-year search.
- * masks[p] points to plane p (n uint64 each). */
+ * masks[p] points to plane p (n uint64 each).  masks[0] (seconds) may be NULL: every spec then fires at second 0, which
+ * is what ParseStandard's 5-field grammar always produces -- 8 bytes per spec less to move.  When every buffer of the
+ * host-pointer form is pinned host memory the kernels work on it in place over PCIe (no staging copies). */
 int b200cron_next_n(b200cron_ctx* ctx, const uint64_t* const masks[6], const int32_t* zone_id, const int64_t* from,
                     size_t n, int k, int64_t* out);
 int b200cron_next_n_dev(b200cron_ctx* ctx, int dev_index, void* stream, const uint64_t* const masks[6],

@@ -434,3 +434,28 @@ def test_device_parse_matches_host_parser(ctx):
     with pytest.raises(api.ParseError):
         ctx.ParseStandardBatch(["TZ=Nope/Nowhere * * * * *"])
     assert ctx.parse_batch([])[0].shape == (6, 0)
+
+
+def test_zero_copy_and_null_seconds_plane(ctx, names):
+    """pinned host buffers are used in place (zero-copy); a NULL seconds plane means second 0 (ParseStandard's output)"""
+    n = 300_001
+    masks = synth.gen_specs(n, seed=9)
+    assert (masks[0] == 1).all()
+    zid = synth.gen_zone_ids(n, len(names), _dst_zones(ctx, names), seed=9)
+    frm = synth.gen_times(n, ts(2024), ts(2034), seed=9)
+    want = po.batch_next_n(masks, frm, 3, zid, names)
+    hm, hf = api.PinnedArray((6, n), np.uint64), api.PinnedArray(n, np.int64)
+    hz, ho = api.PinnedArray(n, np.int32), api.PinnedArray((n, 3), np.int64)
+    hm.array[:] = masks; hf.array[:] = frm; hz.array[:] = zid
+    for five in (False, True):
+        ho.array[:] = 0
+        ctx.next_n(hm.array, hf.array, 3, hz.array, out=ho.array, five_field=five)        # pinned: in place
+        assert np.array_equal(ho.array, want), five
+        assert np.array_equal(ctx.next_n(masks, frm, 3, zid, five_field=five), want), five   # pageable: staged copies
+    w1 = po.batch_next_n(masks, frm, 1)
+    ho1 = api.PinnedArray((n, 1), np.int64)
+    ctx.next_n(hm.array, hf.array, 1, out=ho1.array, five_field=True)
+    assert np.array_equal(ho1.array, w1)
+    with pytest.raises(api.B200CronError):  # error words still come back on the zero-copy path
+        hf.array[0] = 2**62
+        ctx.next_n(hm.array, hf.array, 1, out=ho1.array)
