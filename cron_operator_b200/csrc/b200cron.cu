@@ -466,6 +466,37 @@ extern "C" int b200cron_unmet_since(b200cron_ctx* ctx, const uint64_t* const mas
     return fail(ctx, B200CRON_EINVAL, "unmet_since: NULL required argument");
   std::lock_guard<std::mutex> lk(ctx->mu);
   const int G = (int)ctx->devs.size();
+  {  // zero-copy when every buffer is pinned host memory (see b200cron_next_n)
+    const void* req[] = {masks[0], masks[1], masks[2], masks[3], masks[4], masks[5], earliest, last, next, missed, status, decision};
+    const void* opt[] = {zone_id, policy, active, flags, deadline};
+    bool pinned = n > 0;
+    for (const void* q : req) pinned = pinned && q && is_pinned_host(q);
+    for (const void* q : opt) pinned = pinned && (!q || is_pinned_host(q));
+    if (pinned) {
+      for (int g = 0; g < G; ++g) {
+        Device& d = ctx->devs[g];
+        const Shard sh = shard_of(n, g, G);
+        if (sh.hi <= sh.lo) continue;
+        CU(ctx, cudaSetDevice(d.id));
+        UnmetArgs a{};
+        for (int p = 0; p < 6; ++p) a.m.p[p] = masks[p] + sh.lo;
+        a.zone_id = zone_id ? zone_id + sh.lo : nullptr;
+        a.earliest = earliest + sh.lo; a.now = now; a.now_nsec = now_nsec;
+        a.policy = policy ? policy + sh.lo : nullptr; a.active = active ? active + sh.lo : nullptr;
+        a.flags = flags ? flags + sh.lo : nullptr; a.deadline = deadline ? deadline + sh.lo : nullptr;
+        a.n = sh.hi - sh.lo;
+        a.last = last + sh.lo; a.next = next + sh.lo; a.missed = missed + sh.lo;
+        a.status = status + sh.lo; a.decision = decision + sh.lo;
+        CU(ctx, launch_unmet(ctx, d, d.stream, a));
+        CU(ctx, collect_err(d, d.stream));
+      }
+      for (Device& d : ctx->devs) {
+        CU(ctx, cudaSetDevice(d.id));
+        CU(ctx, cudaStreamSynchronize(d.stream));
+      }
+      return check_err_flags(ctx);
+    }
+  }
   // staging: 6 planes | earliest | deadline | last | next  (8 B) | zone | active | missed (4 B) | policy flags status decision (1 B)
   const size_t per_spec = 10 * 8 + 3 * 4 + 4;
   for (int g = 0; g < G; ++g) {

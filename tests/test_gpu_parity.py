@@ -459,3 +459,20 @@ def test_zero_copy_and_null_seconds_plane(ctx, names):
     with pytest.raises(api.B200CronError):  # error words still come back on the zero-copy path
         hf.array[0] = 2**62
         ctx.next_n(hm.array, hf.array, 1, out=ho1.array)
+
+
+def test_unmet_zero_copy_on_pinned_buffers(ctx, names):
+    n = 50_001
+    masks = synth.gen_specs(n, seed=61, dense_minutes=0.3)
+    zid = synth.gen_zone_ids(n, len(names), _dst_zones(ctx, names), seed=61)
+    now = ts(2026, 3, 29, 12)
+    earliest = now - synth.gen_times(n, 0, 2 * 86400, seed=61)
+    want = ctx.unmet_since(masks, earliest, now, zone_id=zid)  # pageable: staged
+    P = api.PinnedArray
+    hm, he, hz = P((6, n), np.uint64), P(n, np.int64), P(n, np.int32)
+    hm.array[:] = masks; he.array[:] = earliest; hz.array[:] = zid
+    out = dict(last=P(n, np.int64).array, next=P(n, np.int64).array, missed=P(n, np.uint32).array,
+               status=P(n, np.uint8).array, decision=P(n, np.uint8).array)
+    got = ctx.unmet_since(hm.array, he.array, now, zone_id=hz.array, out=out)  # pinned: in place
+    for k in KEYS:
+        assert np.array_equal(got[k], want[k]), k
