@@ -352,7 +352,8 @@ def main():
             "clocks": clocks,
         }
         if world == 1 and not args.no_cpu:
-            reps = 20
+            _, ms1, _ = cpu_reference(2, 1)                      # calibrate: ~12 s of wall time on all host threads
+            reps = int(min(400, max(20, 12_000 / max(ms1, 1e-3))))
             v, ms, threads = cpu_reference(reps, 1)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
                                     "sample": f"full C2 batch ({N_SPECS} specs) x {reps} reps, all host threads; C "
