@@ -198,6 +198,7 @@ struct Walk {
   int32_t pidx;
   int32_t off;
   int64_t ps, pe;
+  int64_t nlo, nhi;  // natural(x) <=> nlo <= x < nhi; recomputed whenever the cached period changes
   // current instant and its civil fields in the zone
   int64_t t;
   int32_t dn;   // local day number
@@ -209,15 +210,20 @@ struct Walk {
   bool dm_ok;
   int32_t tod_last;
 
+  CW_HD void set_natural_range() {
+    // x in [ps, pe) and x - off in [ps, pe)  <=>  ps + max(off, 0) <= x < pe + min(off, 0)
+    nlo = (ps == kAlpha) ? kAlpha : ps + (off > 0 ? off : 0);
+    nhi = (pe == kOmega) ? kOmega : pe + (off < 0 ? off : 0);
+  }
   CW_HD void bind_utc() {
-    zw = nullptr; zo = nullptr; zf = nullptr; zn = 1; pidx = 0; off = 0; ps = kAlpha; pe = kOmega; today_ok = false; dm_ok = false; dm_month = 0; tod_last = 86400;
+    zw = nullptr; zo = nullptr; zf = nullptr; zn = 1; pidx = 0; off = 0; ps = kAlpha; pe = kOmega; nlo = kAlpha; nhi = kOmega; today_ok = false; dm_ok = false; dm_month = 0; tod_last = 86400;
   }
   CW_HD void bind_zone(const ZoneTable& zt, int32_t zone) {
     const int32_t a = CW_LDG(zt.zstart + zone), b = CW_LDG(zt.zstart + zone + 1);
     zw = zt.when + a; zo = zt.off + a; zf = zt.fpre + a; zn = b - a;
-    pidx = -1; off = 0; ps = 1; pe = 0;  // empty cache
+    pidx = -1; off = 0; ps = 1; pe = 0; nlo = 1; nhi = 0;  // empty cache
     today_ok = false; dm_ok = false; dm_month = 0; tod_last = 86400;
-    if (zn == 1) { pidx = 0; off = CW_LDG(zo); ps = kAlpha; pe = kOmega; }
+    if (zn == 1) { pidx = 0; off = CW_LDG(zo); ps = kAlpha; pe = kOmega; nlo = kAlpha; nhi = kOmega; }
   }
 
   // (*Location).lookup(x).offset; moves the cached period to the one containing x
@@ -236,6 +242,7 @@ struct Walk {
     off = CW_LDG(zo + lo);
     ps = CW_LDG(zw + lo);
     pe = (lo + 1 < zn) ? CW_LDG(zw + lo + 1) : kOmega;
+    set_natural_range();
     return off;
   }
 
@@ -270,10 +277,7 @@ struct Walk {
     return x - o;
   }
   // Is local wall time x (as-if-UTC seconds) resolved by Date() to x - off with the current period untouched?
-  CW_HD bool natural(int64_t x) const {
-    const int64_t u = x - off;
-    return x >= ps && x < pe && u >= ps && u < pe;
-  }
+  CW_HD bool natural(int64_t x) const { return x >= nlo && x < nhi; }
 
   // one literal Add(delta) step, 0 < delta <= 3600: inside the period the fields advance with it; across a period
   // edge they are re-derived from the new offset
