@@ -496,3 +496,9 @@ class PinnedArray:
             self.array = None
             lib().b200cron_host_free(self._p)
             self._p = None
+
+    def __del__(self):  # pragma: no cover -- views handed out via .array must not outlive the PinnedArray
+        try:
+            self.free()
+        except Exception:
+            pass

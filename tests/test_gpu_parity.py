@@ -471,8 +471,9 @@ def test_unmet_zero_copy_on_pinned_buffers(ctx, names):
     P = api.PinnedArray
     hm, he, hz = P((6, n), np.uint64), P(n, np.int64), P(n, np.int32)
     hm.array[:] = masks; he.array[:] = earliest; hz.array[:] = zid
-    out = dict(last=P(n, np.int64).array, next=P(n, np.int64).array, missed=P(n, np.uint32).array,
-               status=P(n, np.uint8).array, decision=P(n, np.uint8).array)
+    owners = dict(last=P(n, np.int64), next=P(n, np.int64), missed=P(n, np.uint32), status=P(n, np.uint8),
+                  decision=P(n, np.uint8))  # keep the pinned allocations alive while their views are in use
+    out = {k: v.array for k, v in owners.items()}
     got = ctx.unmet_since(hm.array, he.array, now, zone_id=hz.array, out=out)  # pinned: in place
     for k in KEYS:
         assert np.array_equal(got[k], want[k]), k
