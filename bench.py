@@ -217,6 +217,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-extra", action="store_true", help="skip the C3/C4/C5 kernel-only measurements")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    ap.add_argument("--no-overlap", action="store_true",
+                    help="do not let back-to-back steps overlap (b200cron_ctx_set_overlap off)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":
@@ -270,6 +272,9 @@ def main():
         if rc != 0:
             ctx._check(rc)
 
+    # Steps are independent batches with their own input and output buffers, so a step may start on SMs the previous
+    # step's last wave has left idle (programmatic dependent launch, see b200cron_ctx_set_overlap in the header).
+    ctx.set_overlap(not args.no_overlap)
     for i in range(max(args.warmup, N_BATCH)):
         step(i % N_BATCH)
     ctx.sync_check(stream=st)
@@ -334,6 +339,9 @@ def main():
                        "l2": "inputs larger than L2: steps rotate through 8 distinct 1M-spec batches (512 MB working "
                              "set per GPU), so no step finds its batch in the 126 MB L2",
                        "timing": "one CUDA-event pair on the launch stream around the K back-to-back steps, max over ranks",
+                       "overlap": ("off" if args.no_overlap else "on: the steps are independent batches, so the library "
+                                   "launches them with programmatic stream serialization -- a step's thread blocks "
+                                   "fill SMs while the previous step's last wave drains; ms_per_step = region / K"),
                        "parallelism": f"specs sharded contiguously over {world} GPU(s), no collective"},
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": 48 * N_SPECS, "d2h_bytes_per_step": 8 * N_SPECS,
                     "ms_per_step": e2e_s / e2e_steps * 1e3,

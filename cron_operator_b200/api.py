@@ -108,6 +108,8 @@ def lib():
     L.b200cron_parse_batch_dev.argtypes = [vp, i32, vp, vp, vp, sz, i32, vp, vp, vp, vp]
     L.b200cron_sync_check.restype = i32
     L.b200cron_sync_check.argtypes = [vp, i32, vp]
+    L.b200cron_ctx_set_overlap.restype = i32
+    L.b200cron_ctx_set_overlap.argtypes = [vp, i32]
     L.b200cron_launch_count.restype = C.c_uint64
     L.b200cron_launch_count.argtypes = [vp]
     _LIB = L
@@ -405,6 +407,11 @@ class Context:
                         dev_index: int = 0, stream: int = 0):
         self._check(lib().b200cron_synth_zones_dev(self._h, dev_index, stream or None, seed, start, n, _ptr(pool),
                                                    pool.numel(), p_utc, _ptr(out)))
+
+    def set_overlap(self, on: bool = True):
+        """b200cron_ctx_set_overlap: back-to-back k == 1 next_n_dev launches on one stream may overlap (the caller
+        promises they are independent batches -- see include/b200cron.h)"""
+        self._check(lib().b200cron_ctx_set_overlap(self._h, 1 if on else 0))
 
     def sync_check(self, dev_index: int = 0, stream: int = 0):
         self._check(lib().b200cron_sync_check(self._h, dev_index, stream or None))

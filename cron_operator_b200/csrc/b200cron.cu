@@ -36,6 +36,17 @@ struct Slot {
   size_t cap = 0;
 };
 
+// Compact index list through which the easy unmet kernel hands Crons to the general one.  `done` is recorded after
+// the pair that used the list; the next pair to use it waits on that event first, so calls on different streams
+// never share a list that is still in flight.
+struct DeferList {
+  uint32_t* idx = nullptr;
+  uint32_t* count = nullptr;
+  size_t cap = 0;  // entries
+  cudaEvent_t done = nullptr;
+};
+constexpr int kDeferLists = 3;
+
 struct Device {
   int id = 0;
   cudaStream_t stream = nullptr;  // default stream of the _dev entry points
@@ -48,6 +59,8 @@ struct Device {
   Slot slots[kSlots];
   uint64_t* d_scratch = nullptr;  // per-tile sums of the unmet-list prefix sum
   size_t scratch_cap = 0;         // entries
+  DeferList defer[kDeferLists];       // scratch of the unmet kernel pair, handed out round-robin (see launch_unmet)
+  int defer_next = 0;
   uint64_t* d_static_sums = nullptr;  // device address of g_static_tile_sums on this device (resolved on first use)
   ZoneTable zt{};
 };
@@ -60,6 +73,7 @@ struct b200cron_ctx {
   std::string error;
   std::mutex mu;
   std::atomic<uint64_t> launches{0};
+  std::atomic<int> overlap{0};  // b200cron_ctx_set_overlap
 };
 
 namespace {
@@ -128,9 +142,17 @@ cudaError_t launch_next(b200cron_ctx* ctx, const Device& d, cudaStream_t st, con
   ctx->launches.fetch_add(1, std::memory_order_relaxed);
   if (k == 1 && !getenv("B200CRON_NEXT1_PAIRED")) {  // one spec per lane (finer waves); the env var selects the paired kernel
     const unsigned g1 = (unsigned)((n + kNext1Threads - 1) / kNext1Threads);
-    if (zone) next1_kernel<false><<<g1, kNext1Threads, 0, st>>>(m, zone, from, n, out, d.zt, d.d_err);
-    else next1_kernel<true><<<g1, kNext1Threads, 0, st>>>(m, zone, from, n, out, d.zt, d.d_err);  // all-UTC launch
-    return cudaGetLastError();
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(g1);
+    cfg.blockDim = dim3(kNext1Threads);
+    cfg.stream = st;
+    cudaLaunchAttribute attr{};
+    attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr.val.programmaticStreamSerializationAllowed = 1;
+    if (ctx->overlap.load(std::memory_order_relaxed)) { cfg.attrs = &attr; cfg.numAttrs = 1; }
+    int* err = d.d_err;
+    if (zone) return cudaLaunchKernelEx(&cfg, next1_kernel<false>, m, zone, from, n, out, d.zt, err);
+    return cudaLaunchKernelEx(&cfg, next1_kernel<true>, m, zone, from, n, out, d.zt, err);  // all-UTC launch
   }
   switch (k) {
     case 1: return launch_next_kt<1>(vec, grid, smem, st, m, zone, from, n, k, out, d.zt, d.d_err);
@@ -143,12 +165,42 @@ cudaError_t launch_next(b200cron_ctx* ctx, const Device& d, cudaStream_t st, con
   }
 }
 
-cudaError_t launch_unmet(b200cron_ctx* ctx, const Device& d, cudaStream_t st, const UnmetArgs& a) {
+cudaError_t launch_unmet(b200cron_ctx* ctx, Device& d, cudaStream_t st, const UnmetArgs& a) {
   if (a.n == 0) return cudaSuccess;
   const unsigned grid = (unsigned)((a.n + kUnmetThreads - 1) / kUnmetThreads);
-  ctx->launches.fetch_add(1, std::memory_order_relaxed);
-  unmet_kernel<<<grid, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err);
-  return cudaGetLastError();
+  static const bool single = getenv("B200CRON_UNMET_SINGLE") != nullptr;  // one general kernel, no scratch (tuning)
+  if (single || a.n > 0xffffffffULL) {
+    ctx->launches.fetch_add(1, std::memory_order_relaxed);
+    unmet_kernel<kUnmetSingle><<<grid, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, nullptr, nullptr);
+    return cudaGetLastError();
+  }
+  DeferList& b = d.defer[d.defer_next];
+  d.defer_next = (d.defer_next + 1) % kDeferLists;
+  cudaError_t e;
+  if (!b.done) {
+    if ((e = cudaEventCreateWithFlags(&b.done, cudaEventDisableTiming)) != cudaSuccess) return e;
+    if ((e = cudaMalloc(&b.count, sizeof(uint32_t))) != cudaSuccess) return e;
+  } else if ((e = cudaStreamWaitEvent(st, b.done, 0)) != cudaSuccess) {
+    return e;
+  }
+  if (a.n > b.cap) {  // every Cron of the launch may be deferred
+    if (b.idx) {
+      if ((e = cudaEventSynchronize(b.done)) != cudaSuccess) return e;
+      if ((e = cudaFree(b.idx)) != cudaSuccess) return e;
+      b.idx = nullptr;
+      b.cap = 0;
+    }
+    if ((e = cudaMalloc(&b.idx, a.n * sizeof(uint32_t))) != cudaSuccess) return e;
+    b.cap = a.n;
+  }
+  if ((e = cudaMemsetAsync(b.count, 0, sizeof(uint32_t), st)) != cudaSuccess) return e;
+  ctx->launches.fetch_add(2, std::memory_order_relaxed);
+  unmet_kernel<kUnmetEasy><<<grid, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, b.idx, b.count);
+  if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  const unsigned hard_grid = grid < 148u * 12u ? grid : 148u * 12u;
+  unmet_hard_kernel<<<hard_grid, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, b.idx, b.count);
+  if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  return cudaEventRecord(b.done, st);
 }
 
 cudaError_t launch_history(b200cron_ctx* ctx, cudaStream_t st, const uint64_t* seg_off, const int64_t* key,
@@ -288,6 +340,11 @@ extern "C" void b200cron_ctx_destroy(b200cron_ctx* ctx) {
     if (d.d_zstart) cudaFree(d.d_zstart);
     if (d.d_err) cudaFree(d.d_err);
     if (d.d_scratch) cudaFree(d.d_scratch);
+    for (DeferList& b : d.defer) {
+      if (b.idx) cudaFree(b.idx);
+      if (b.count) cudaFree(b.count);
+      if (b.done) cudaEventDestroy(b.done);
+    }
     if (d.h_err) cudaFreeHost(d.h_err);
   }
   delete ctx;
@@ -343,6 +400,12 @@ extern "C" uint64_t b200cron_launch_count(const b200cron_ctx* ctx) { return ctx 
 // =================================================================================================================
 // Next / NextN
 // =================================================================================================================
+extern "C" int b200cron_ctx_set_overlap(b200cron_ctx* ctx, int on) {
+  if (!ctx) return B200CRON_EINVAL;
+  ctx->overlap.store(on ? 1 : 0, std::memory_order_relaxed);
+  return B200CRON_OK;
+}
+
 extern "C" int b200cron_next_n_dev(b200cron_ctx* ctx, int dev_index, void* stream, const uint64_t* const masks[6],
                                    const int32_t* zone_id, const int64_t* from, size_t n, int k, int64_t* out) {
   Device* d = device_at(ctx, dev_index);

@@ -267,6 +267,20 @@ struct Walk {
     dm_ok = false;
   }
 
+  // load() for a walk bound to UTC: no period lookup
+  CW_HD void load_utc(int64_t tt) {
+    t = tt;
+    const int32_t hi = (int32_t)(tt >> 7);
+    int32_t q = hi / 675;
+    int32_t r = hi - q * 675;
+    if (r < 0) { r += 675; q -= 1; }
+    dn = q;
+    sod = r * 128 + (int32_t)(tt & 127);
+    civil_from_days(dn, Y, M, D);
+    today_ok = false;
+    dm_ok = false;
+  }
+
   // time.Date(y, mo, d, h, mi, s, 0, loc): as-if-UTC seconds, then the two-lookup offset resolution
   CW_HD int64_t go_date(int32_t y, int32_t mo, int32_t d, int32_t sod_) {
     int32_t m0 = mo - 1;
@@ -535,13 +549,15 @@ CW_HD int32_t next_tod_ge(const Spec& s, int32_t sod) {
 // T, the hour loop simply continues with the shifted hour), so the walk equals: nothing matched in [sod, local(T)),
 // then the first matching time of day >= local(T) + d in the new period.  Anything else (sub-hour shifts, midnight
 // transitions, no fire left that day) is left to the step emulation.
+template <bool kUtcOnly = false>
 CW_HD bool find_tod_today(const Spec& s, Walk& w, int64_t t, int32_t sod, int64_t* r, int32_t* rsod) {
   const int32_t tod = next_tod_ge(s, sod);
-  if (tod >= 0 && t + (tod - sod) < w.pe) {
+  if (tod >= 0 && (kUtcOnly || t + (tod - sod) < w.pe)) {
     *r = t + (tod - sod);
     *rsod = tod;
     return true;
   }
+  if (kUtcOnly) return false;  // one endless period: no fire left today
   if (w.pe - t >= 86400 - sod) return false;  // the period outlives the day: no fire left today (tod < 0)
   if (w.pidx < 0 || w.pidx + 1 >= w.zn) return false;
   const int32_t sod_t = sod + (int32_t)(w.pe - t);  // local time of day at which the transition strikes (< 86400)
@@ -597,7 +613,7 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
       const int32_t k = Dn - w.D;
       const int64_t x1 = (int64_t)(w.dn + 1) * 86400, xk = (int64_t)(w.dn + k) * 86400;
       const int64_t r = xk - w.off + s.tod1;
-      if (w.t + (86400 - sod) < w.pe && w.natural(x1) && w.natural(xk) && r < w.pe) {
+      if (kUtcOnly || (w.t + (86400 - sod) < w.pe && w.natural(x1) && w.natural(xk) && r < w.pe)) {
         w.t = r;
         w.dn += k; w.D = Dn; w.sod = s.tod1;
         *out = r;
@@ -626,7 +642,7 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
     if (sod <= w.tod_last) {  // (chained calls know the day's last fire: past it there is nothing to search)
       int64_t r;
       int32_t rsod;
-      if (find_tod_today(s, w, w.t, sod, &r, &rsod)) {
+      if (find_tod_today<kUtcOnly>(s, w, w.t, sod, &r, &rsod)) {
         w.t = r;
         w.sod = rsod;
         w.today_ok = true;
@@ -635,7 +651,7 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
         return true;
       }
     }
-    if (w.t + (86400 - sod) >= w.pe) return false;  // the Hour()==0 wrap must happen inside this period
+    if (!kUtcOnly && w.t + (86400 - sod) >= w.pe) return false;  // the Hour()==0 wrap must happen inside this period
   }
   if (!have_dm) {
     leap = is_leap(w.Y);
@@ -683,7 +699,7 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
   const int64_t x_mid = (int64_t)found_dn * 86400;            // local midnight of the fire day
   if (!zoned) {
     if (!found) { *out = kZero; return true; }
-    w.t = x_mid + s.tod1 - w.off;
+    w.t = x_mid + s.tod1 - (kUtcOnly ? 0 : w.off);
     w.dn = found_dn; w.sod = s.tod1; w.Y = Yc; w.M = Mc; w.D = Dc;
     w.today_ok = true;
     w.dm_month = dm_found; w.dm_ok = true;
@@ -733,9 +749,11 @@ CW_HD bool next_try(const Spec& s, Walk& w, int64_t t, bool resident, int64_t* o
   CW_COUNT(next);
   if (s.never) { *out = kZero; return true; }
   const int64_t t1 = t + 1;
-  if (resident && t1 < w.pe && w.sod + 1 < 86400) {
+  if (resident && (kUtcOnly || t1 < w.pe) && w.sod + 1 < 86400) {
     w.t = t1;
     w.sod += 1;
+  } else if (kUtcOnly) {
+    w.load_utc(t1);
   } else {
     w.load(t1);
   }
@@ -780,8 +798,9 @@ CW_HD int64_t next_slow(const Spec& s, Walk& w) {
 }
 template <bool kOutline, bool kUtcOnly = false>
 CW_HD int64_t next_from_t(const Spec& s, Walk& w, int64_t t, bool resident) {
-  int64_t r;
-  if (next_try<kUtcOnly>(s, w, t, resident, &r)) return r;
+  int64_t r = kZero;
+  // in UTC the closed form always answers (one endless period, every Date() natural): no step emulation in the kernel
+  if (next_try<kUtcOnly>(s, w, t, resident, &r) || kUtcOnly) return r;
   return next_slow<kOutline>(s, w);
 }
 CW_HD int64_t next_from(const Spec& s, Walk& w, int64_t t, bool resident) { return next_from_t<false>(s, w, t, resident); }

@@ -48,6 +48,9 @@ __device__ __forceinline__ bool bind_checked(Walk& w, const ZoneTable& zt, int32
 //   KT = 0 (any other k): transposed staging [j][row] and a division per element on the way out.
 // Algorithmic bytes: 48 (masks) + 8 (from) [+ 4 zone] in, 8k out per spec.
 // -------------------------------------------------------------------------------------------------------------
+#ifndef B200CRON_NEXTN_OUTLINE
+#define B200CRON_NEXTN_OUTLINE 0  // 1: the step emulation is called out of line (smaller loop body) -- tuning
+#endif
 constexpr int kNextThreads = 64;
 constexpr int kNextWarpTile = 64;
 constexpr int kNextTile = kNextWarpTile * (kNextThreads / 32);
@@ -117,7 +120,7 @@ next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* 
       // iteration run ahead and the warp executes each path of each iteration separately.
       __syncwarp();
       if (ok && t != kZero) {
-        t = cronwalk::next_from(ss, w, t, j > 0);
+        t = cronwalk::next_from_t<B200CRON_NEXTN_OUTLINE != 0>(ss, w, t, j > 0);
         // chained calls keep walking: re-check the zoned horizon (UTC never trips it)
         if (KT != 1 && t != kZero && w.zn > 1 && t >= zt.horizon - kSixYears) { atomicOr(err, kErrRange); ok = false; t = kZero; }
       } else {
@@ -174,12 +177,16 @@ template <bool kUtcOnly>
 __global__ void __launch_bounds__(kNext1Threads, B200CRON_NEXT1_MINBLOCKS)
 next1_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* __restrict__ from, size_t n,
              int64_t* __restrict__ out, ZoneTable zt, int* __restrict__ err) {
+  // Programmatic dependent launch: when the host marks consecutive launches as independent
+  // (b200cron_ctx_set_overlap), the next launch on the stream may start filling SMs as soon as every CTA of this one
+  // has got this far, instead of idling through this launch's last partial wave.  A no-op for ordinary launches.
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const size_t i = (size_t)blockIdx.x * kNext1Threads + threadIdx.x;
   if (i >= n) return;
   const Spec s = cronwalk::make_spec(m.p[0] ? __ldg(m.p[0] + i) : 1ULL, __ldg(m.p[1] + i), __ldg(m.p[2] + i), __ldg(m.p[3] + i),
                                      __ldg(m.p[4] + i), __ldg(m.p[5] + i));
   const int64_t t = __ldg(from + i);
-  const int32_t zone = zone_id ? __ldg(zone_id + i) : 0;
+  const int32_t zone = (!kUtcOnly && zone_id) ? __ldg(zone_id + i) : 0;
   Walk w;
   const bool ok = bind_checked(w, zt, zone, t, err);
   out[i] = ok ? cronwalk::next_from_t<false, kUtcOnly>(s, w, t, false) : kZero;
@@ -212,9 +219,31 @@ struct UnmetArgs {
 
 // 12 CTAs/SM (40 registers, some spills): the kernel is bound by instruction-fetch redirects in branchy, divergent
 // code (ncu: 21 % issue-active at 24 warps/SM); more resident warps hide them -- measured 8.3 -> 6.9 ms per 10M Crons.
-__global__ void __launch_bounds__(kUnmetThreads, 12) unmet_kernel(UnmetArgs a, ZoneTable zt, int* __restrict__ err) {
-  const size_t i = (size_t)blockIdx.x * kUnmetThreads + threadIdx.x;
-  const bool live = i < a.n;
+//
+// Modes.  kUnmetSingle: one launch does everything.  kUnmetEasy + kUnmetHard (the default pair): the easy kernel lets
+// only the closed form answer, gives every Cron at most kUnmetEasyRounds rounds (first fire + fast-forward, end of
+// chain, Next(now)) and appends the Crons that need more -- a zone transition in the way, a step only the emulation
+// can take -- to a compact index list; the hard kernel then runs the general state machine over that list only, in
+// dense warps.  On the C4 workload 8 % of the Crons are deferred (all zoned; 2.4 % need the step emulation, which in
+// the single kernel made every second warp run it for one or two lanes).  The easy kernel has no step emulation in
+// its instruction stream and its lanes stay together.
+enum { kUnmetSingle = 0, kUnmetEasy = 1, kUnmetHard = 2 };
+#ifndef B200CRON_UNMET_EASY_ROUNDS
+#define B200CRON_UNMET_EASY_ROUNDS 3
+#endif
+constexpr int kUnmetEasyRounds = B200CRON_UNMET_EASY_ROUNDS;
+#ifndef B200CRON_UNMET_EASY_MINBLOCKS
+#define B200CRON_UNMET_EASY_MINBLOCKS 12
+#endif
+#ifndef B200CRON_UNMET_HARD_MINBLOCKS
+#define B200CRON_UNMET_HARD_MINBLOCKS 12
+#endif
+
+// one Cron per lane; all 32 lanes of the warp must call this together (live = false for padding lanes)
+template <int kMode>
+__device__ __forceinline__ void unmet_one(const UnmetArgs& a, const ZoneTable& zt, int* __restrict__ err, size_t i,
+                                          bool live, uint32_t* __restrict__ defer_idx,
+                                          uint32_t* __restrict__ defer_count) {
   const size_t ii = live ? i : 0;  // out-of-range lanes stay in the warp-uniform loop below, doing nothing
   const Spec s = cronwalk::make_spec(__ldg(a.m.p[0] + ii), __ldg(a.m.p[1] + ii), __ldg(a.m.p[2] + ii),
                                      __ldg(a.m.p[3] + ii), __ldg(a.m.p[4] + ii), __ldg(a.m.p[5] + ii));
@@ -245,15 +274,56 @@ __global__ void __launch_bounds__(kUnmetThreads, 12) unmet_kernel(UnmetArgs a, Z
   st.w.bind_utc();
   if (ok) cronwalk::unmet_begin(zt, zone, in, st);
   // all 32 lanes go round together: a full-mask vote per iteration is the reconvergence point
-  while (__any_sync(0xffffffffu, !st.done)) {
-    if (!st.done) cronwalk::unmet_step(s, in, st);
+  bool defer = false;
+  if (kMode == kUnmetEasy) {
+#pragma unroll 1
+    for (int round = 0; round < kUnmetEasyRounds; ++round) {
+      if (!__any_sync(0xffffffffu, !st.done)) break;
+      if (!st.done) cronwalk::unmet_step_easy(s, in, st, &defer);
+    }
+    defer = defer || !st.done;  // still going after kUnmetEasyRounds rounds: a longer chain, the general kernel's business
+    // warp-aggregated append of the deferred Crons to the compact list (ballot + prefix popcount, one atomic per warp)
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned mask = __ballot_sync(0xffffffffu, defer);
+    if (mask) {
+      const int leader = __ffs((int)mask) - 1;
+      uint32_t base = 0;
+      if ((int)lane == leader) base = atomicAdd(defer_count, (uint32_t)__popc(mask));
+      base = __shfl_sync(0xffffffffu, base, leader);
+      if (defer) defer_idx[base + (uint32_t)__popc(mask & ((1u << lane) - 1u))] = (uint32_t)i;
+    }
+  } else {
+    while (__any_sync(0xffffffffu, !st.done)) {
+      if (!st.done) cronwalk::unmet_step(s, in, st);
+    }
   }
-  if (live) {
+  if (live && !defer) {
     a.last[i] = st.o.last;
     a.next[i] = st.o.next;
     a.missed[i] = st.o.missed;
     a.status[i] = st.o.status;
     a.decision[i] = st.o.decision;
+  }
+}
+
+template <int kMode>
+__global__ void __launch_bounds__(kUnmetThreads, kMode == kUnmetEasy ? B200CRON_UNMET_EASY_MINBLOCKS : 12)
+unmet_kernel(UnmetArgs a, ZoneTable zt, int* __restrict__ err, uint32_t* __restrict__ defer_idx,
+             uint32_t* __restrict__ defer_count) {
+  const size_t i = (size_t)blockIdx.x * kUnmetThreads + threadIdx.x;
+  unmet_one<kMode>(a, zt, err, i, i < a.n, defer_idx, defer_count);
+}
+
+// the general state machine over the compact list the easy kernel left behind (grid-stride: the host does not know
+// the list's length when it launches)
+__global__ void __launch_bounds__(kUnmetThreads, B200CRON_UNMET_HARD_MINBLOCKS)
+unmet_hard_kernel(UnmetArgs a, ZoneTable zt, int* __restrict__ err, const uint32_t* __restrict__ defer_idx,
+                  const uint32_t* __restrict__ defer_count) {
+  const uint32_t cnt = *defer_count;
+  for (size_t base = (size_t)blockIdx.x * kUnmetThreads; base < cnt; base += (size_t)gridDim.x * kUnmetThreads) {
+    const size_t q = base + threadIdx.x;
+    const bool live = q < cnt;
+    unmet_one<kUnmetHard>(a, zt, err, live ? defer_idx[q] : 0, live, nullptr, nullptr);
   }
 }
 

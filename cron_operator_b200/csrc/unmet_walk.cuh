@@ -254,6 +254,36 @@ CW_HD void unmet_step(const Spec& s, const UnmetIn& in, UnmetState& st) {
   st.resident = true;
 }
 
+
+// unmet_step for the "easy" kernel: same bookkeeping, but only the closed form may answer.  Whenever the step
+// emulation would be needed, or a chained call steps backwards (the cycle guard's business), the Cron is handed to
+// the general kernel (*defer) and recomputed there from scratch.
+CW_HD void unmet_step_easy(const Spec& s, const UnmetIn& in, UnmetState& st, bool* defer) {
+  int64_t t;
+  if (!next_try(s, st.w, st.arg, st.resident, &t)) { *defer = true; st.done = true; return; }
+  if (st.final_phase) {
+    st.o.next = t;
+    unmet_finish(in, st);
+    return;
+  }
+  if (st.prev != kZero && t != kZero && t <= st.prev) { *defer = true; st.done = true; return; }
+  if (t == kZero) {  // :410-412
+    st.o.last = kZero; st.o.missed = 0; st.o.status = kStUnschedulable; st.o.decision = kDecErrUnschedulable;
+    st.done = true;
+    return;
+  }
+  if (t > in.now) {  // the chain is over: one more call, from now
+    st.final_phase = true; st.arg = in.now; st.resident = false;
+    return;
+  }
+  st.o.missed = sat_add(st.o.missed, 1);
+  chain_fast_forward(s, st.w, in.now, &st.o.missed);
+  st.o.last = st.w.t;
+  st.prev = st.w.t;
+  st.arg = st.prev;
+  st.resident = true;
+}
+
 CW_HD UnmetOut unmet_decide(const Spec& s, const ZoneTable& zt, int32_t zone, const UnmetIn& in) {
   UnmetState st;
   unmet_begin(zt, zone, in, st);

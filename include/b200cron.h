@@ -137,6 +137,16 @@ int b200cron_next_n(b200cron_ctx* ctx, const uint64_t* const masks[6], const int
 int b200cron_next_n_dev(b200cron_ctx* ctx, int dev_index, void* stream, const uint64_t* const masks[6],
                         const int32_t* zone_id, const int64_t* from, size_t n, int k, int64_t* out);
 
+/* Batches of specs are independent of each other (the reference evaluates every Cron in its own Reconcile call,
+ * cron_controller.go:90), so back-to-back k == 1 launches need not wait for each other.  With on != 0 a
+ * b200cron_next_n_dev launch (k == 1) may begin while the previous k == 1 launch on the same stream is still
+ * draining its last wave of thread blocks (programmatic dependent launch).  The caller promises that such a launch
+ * does not read what the previous one writes (e.g. does not pass its `out` as the next `from`) and that whatever
+ * produced its inputs on that stream was followed by some other operation (an event record, a copy, any other
+ * kernel).  Everything else -- k > 1, other entry points, other work queued on the stream -- still runs in stream
+ * order after both have finished.  Off by default. */
+int b200cron_ctx_set_overlap(b200cron_ctx* ctx, int on);
+
 /* ---- unmet-schedule enumeration + concurrency decision -------------------------------------------------------- */
 
 /* Replaces getNextSchedule (cron_controller.go:389-437) and the gates + Allow/Forbid/Replace decision of Reconcile

@@ -61,7 +61,8 @@ void shim_next_n(void* table, const uint64_t* const masks[6], const int32_t* zon
     bool resident = false;
     for (int q = 0; q < k; ++q) {
       if (t != kZero) {
-        t = next_from(s, w, t, resident);
+        // zone_id == NULL: the all-UTC specialisation, as next1_kernel<true> is chosen for launches without zone ids
+        t = zone_id ? next_from(s, w, t, resident) : next_from_t<false, true>(s, w, t, resident);
         resident = true;
       }
       out[i * (size_t)k + q] = t;
@@ -86,6 +87,50 @@ void shim_unmet(void* table, const uint64_t* const masks[6], const int32_t* zone
     in.deadline = deadline ? deadline[i] : kZero;
     UnmetOut o = unmet_decide(s, zt, zone_id ? zone_id[i] : 0, in);
     last[i] = o.last; next[i] = o.next; missed[i] = o.missed; status[i] = o.status; decision[i] = o.decision;
+  }
+}
+
+// The two-phase scheme of unmet_kernel: `easy_rounds` rounds of unmet_step_easy, and the general state machine from
+// scratch for the Crons that did not finish.  rounds[i] = easy rounds used, deferred[i] = 1 when the general machine
+// had to answer.  (easy_rounds <= 0: the general machine alone; rounds[i] then counts its steps.)
+void shim_unmet_two_phase(void* table, const uint64_t* const masks[6], const int32_t* zone_id, const int64_t* earliest,
+                          int64_t now, int32_t now_nsec, const uint8_t* policy, const uint32_t* active,
+                          const uint8_t* flags, const int64_t* deadline, size_t n, int easy_rounds, int64_t* last,
+                          int64_t* next, uint32_t* missed, uint8_t* status, uint8_t* decision, uint8_t* rounds,
+                          uint8_t* deferred) {
+  ZoneTable zt = view(table);
+  for (size_t i = 0; i < n; ++i) {
+    Spec s = make_spec(masks[0][i], masks[1][i], masks[2][i], masks[3][i], masks[4][i], masks[5][i]);
+    UnmetIn in;
+    in.earliest = earliest[i];
+    in.now = now;
+    in.now_nsec = now_nsec;
+    in.policy = policy ? policy[i] : 0;
+    in.active = active ? active[i] : 0;
+    in.flags = flags ? flags[i] : 0;
+    in.deadline = deadline ? deadline[i] : kZero;
+    const int32_t z = zone_id ? zone_id[i] : 0;
+    UnmetState st;
+    unmet_begin(zt, z, in, st);
+    bool defer = false;
+    int r = 0;
+    if (easy_rounds > 0) {
+      while (!st.done) {
+        if (r >= easy_rounds) { defer = true; break; }
+        unmet_step_easy(s, in, st, &defer);
+        ++r;
+      }
+    } else {
+      defer = !st.done;
+    }
+    if (defer) {
+      unmet_begin(zt, z, in, st);
+      int g = 0;
+      while (!st.done) { unmet_step(s, in, st); ++g; }
+      if (easy_rounds <= 0) r = g > 255 ? 255 : g;
+    }
+    rounds[i] = (uint8_t)r; deferred[i] = defer ? 1 : 0;
+    last[i] = st.o.last; next[i] = st.o.next; missed[i] = st.o.missed; status[i] = st.o.status; decision[i] = st.o.decision;
   }
 }
 

@@ -36,6 +36,8 @@ def lib():
         L.shim_unmet.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p,
                                  C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p,
                                  C.c_void_p, C.c_void_p]
+        L.shim_unmet_two_phase.argtypes = ([C.c_void_p] * 4 + [C.c_int64, C.c_int32] + [C.c_void_p] * 4 +
+                                           [C.c_size_t, C.c_int] + [C.c_void_p] * 7)
         _LIB = L
     return _LIB
 
@@ -95,3 +97,23 @@ def unmet(masks, earliest, now, now_nsec=0, policy=None, active=None, flags=None
                      _p(flags), _p(deadline), n, last.ctypes.data, nxt.ctypes.data, missed.ctypes.data,
                      status.ctypes.data, decision.ctypes.data)
     return dict(last=last, next=nxt, missed=missed, status=status, decision=decision)
+
+
+def unmet_two_phase(masks, earliest, now, easy_rounds, now_nsec=0, policy=None, active=None, flags=None, deadline=None,
+                    zone_id=None, t=None):
+    """the kernels' easy/hard split: `easy_rounds` closed-form rounds, then the general machine for what is left;
+    also returns rounds (easy rounds used) and deferred (1 = answered by the general machine)"""
+    t = t or table()
+    n = masks.shape[1]
+    earliest = np.ascontiguousarray(earliest, dtype=np.int64)
+    cv = lambda a, dt: None if a is None else np.ascontiguousarray(a, dtype=dt)  # noqa: E731
+    zid, policy, active = cv(zone_id, np.int32), cv(policy, np.uint8), cv(active, np.uint32)
+    flags, deadline = cv(flags, np.uint8), cv(deadline, np.int64)
+    last, nxt = np.empty(n, np.int64), np.empty(n, np.int64)
+    missed, status, decision = np.empty(n, np.uint32), np.empty(n, np.uint8), np.empty(n, np.uint8)
+    rounds, deferred = np.empty(n, np.uint8), np.empty(n, np.uint8)
+    lib().shim_unmet_two_phase(t, _planes(masks), _p(zid), earliest.ctypes.data, now, now_nsec, _p(policy), _p(active),
+                               _p(flags), _p(deadline), n, easy_rounds, last.ctypes.data, nxt.ctypes.data,
+                               missed.ctypes.data, status.ctypes.data, decision.ctypes.data, rounds.ctypes.data,
+                               deferred.ctypes.data)
+    return dict(last=last, next=nxt, missed=missed, status=status, decision=decision, rounds=rounds, deferred=deferred)

@@ -164,3 +164,42 @@ def test_upstream_hangs_are_reported_not_reproduced():
     want = po.batch_unmet(m, np.array([1838162695]), 1839851648, zone_id=zz, zone_names=NAMES)
     _cmp(got, want)
     assert got["status"][0] == po.ST_NONTERMINATING and got["decision"][0] == po.DEC_ERR_UNSCHEDULABLE
+
+
+@pytest.mark.parametrize("easy_rounds", [1, 3, 5])
+def test_easy_hard_split_equals_general_machine(easy_rounds):
+    """unmet_kernel<easy> + unmet_hard_kernel: closed-form rounds first, the general machine (from scratch) for the
+    Crons left over -- same answers as the general machine alone, which the tests above pin to the oracle"""
+    n = 60000
+    masks = synth.gen_specs(n, seed=41, dense_minutes=0.5)
+    dst = [z for z in range(1, len(NAMES)) if (shim.zone_entries(z)[0] > ts(2030)).any()]
+    zid = synth.gen_zone_ids(n, len(NAMES), np.array(dst), seed=41)
+    now = ts(2026, 3, 29, 12)
+    earliest = now - 30 * 86400 + synth.gen_times(n, -86400, 86400, seed=41)
+    earliest[::97] = now + 5  # earliest after now: straight to Next(now)
+    rng = np.random.default_rng(5)
+    policy = rng.integers(0, 3, n).astype(np.uint8)
+    active = rng.integers(0, 3, n).astype(np.uint32)
+    flags = (rng.random(n) < 0.03).astype(np.uint8) * rng.integers(1, 3, n).astype(np.uint8)
+    deadline = np.where(rng.random(n) < 0.01, now - 100, po.ZERO).astype(np.int64)
+    want = shim.unmet(masks, earliest, now, 0, policy, active, flags, deadline, zone_id=zid)
+    got = shim.unmet_two_phase(masks, earliest, now, easy_rounds, 0, policy, active, flags, deadline, zone_id=zid)
+    _cmp(got, want)
+    frac = got["deferred"].mean()
+    assert 0 < frac < (1.0 if easy_rounds == 1 else 0.2), frac
+    # transition windows of the edge zones, and the cycle upstream hangs on
+    texts = ["*/20 * * * *", "30 2 * * *", "0 0 * * *", "59 23 * * *", "0 0 1 * *", "*/30 0-4 * * *"]
+    base = _masks_of(texts)
+    for name in EDGE_ZONES:
+        z = NAMES.index(name)
+        when, _ = shim.zone_entries(z)
+        for t in [int(w) for w in when if ts(2021) < w < ts(2041)][:8]:
+            for a, b in [(-3 * 86400, 3 * 86400), (-40 * 86400, 1), (-7200, 7200), (-20 * 86400, 20 * 86400)]:
+                zz = np.full(len(texts), z, np.int32)
+                _cmp(shim.unmet_two_phase(base, np.full(len(texts), t + a), t + b, easy_rounds, zone_id=zz),
+                     shim.unmet(base, np.full(len(texts), t + a), t + b, zone_id=zz), (name, t, a, b))
+    z = NAMES.index("Pacific/Chatham")
+    m = np.array([[0x1], [0x800010000100001], [0x8], [0x80000000FFFFFFFE], [0x8000000000001FFE], [0x11]], dtype=np.uint64)
+    zz = np.array([z], np.int32)
+    got = shim.unmet_two_phase(m, np.array([1838162695]), 1839851648, easy_rounds, zone_id=zz)
+    assert got["status"][0] == po.ST_NONTERMINATING and got["deferred"][0] == 1

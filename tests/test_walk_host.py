@@ -63,6 +63,19 @@ def test_next_n_utc_with_seconds():
     assert np.array_equal(got, want)
 
 
+def test_utc_specialisation_equals_general_walk():
+    """no zone ids -> the all-UTC instantiation (next1_kernel<true>); zone id 0 everywhere -> the general walk bound to
+    UTC.  Same answers, and the oracle's, for single and chained calls."""
+    n = 30000
+    for with_seconds, k, seed in [(False, 1, 21), (True, 5, 22)]:
+        masks = synth.gen_specs(n, seed=seed, with_seconds=with_seconds)
+        frm = synth.gen_times(n, ts(2024), ts(2036), seed=seed)
+        a = shim.next_n(masks, frm, k=k)
+        b = shim.next_n(masks, frm, k=k, zone_id=np.zeros(n, np.int32))
+        assert np.array_equal(a, b)
+        assert np.array_equal(a[:3000], po.batch_next_n(masks[:, :3000].copy(), frm[:3000], k=k))
+
+
 def test_next_extreme_times_utc():
     texts = ["* * * * *", "0 0 29 2 *", "59 23 31 12 *", "0 0 1 1 *", "*/7 */5 * * 1"]
     masks = _masks_of(texts)
