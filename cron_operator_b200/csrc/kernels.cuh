@@ -51,6 +51,9 @@ __device__ __forceinline__ bool bind_checked(Walk& w, const ZoneTable& zt, int32
 #ifndef B200CRON_NEXTN_OUTLINE
 #define B200CRON_NEXTN_OUTLINE 0  // 1: the step emulation is called out of line (smaller loop body) -- tuning
 #endif
+#ifndef B200CRON_NEXTN_SORT
+#define B200CRON_NEXTN_SORT 1  // 0: walk the tile's specs in input order (tuning)
+#endif
 constexpr int kNextThreads = 64;
 constexpr int kNextWarpTile = 64;
 constexpr int kNextTile = kNextWarpTile * (kNextThreads / 32);
@@ -61,6 +64,7 @@ next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* 
               int64_t* __restrict__ out, ZoneTable zt, int* __restrict__ err) {
   extern __shared__ __align__(16) int64_t stage_all[];  // [warps][64 * k], unused when KT == 1
   const int k = KT > 0 ? KT : k_rt;
+  constexpr bool kSortTile = KT >= 8 && B200CRON_NEXTN_SORT != 0;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const size_t wbase = (size_t)blockIdx.x * kNextTile + (size_t)warp * kNextWarpTile;
   if (wbase >= n) return;
@@ -97,6 +101,55 @@ next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* 
     }
   }
 
+  // Divergence control for long chains (KT >= 8): the cost of one chained call depends on how often the spec fires --
+  // several times a day (next time of day on the resident day), once a day or less (next matching day), in between.
+  // A warp pays for every path any of its lanes takes, so the tile's 64 specs are dealt out by class: the warp's
+  // first pass walks the 32 that fire most often, the second pass the rest, and at most one pass mixes classes.
+  // The specs travel through the (still unused) output staging buffer; results are staged by original row, so the
+  // output order does not change.
+  int rows2[2] = {2 * lane, 2 * lane + 1};
+  if (kSortTile) {
+    __shared__ uint8_t s_rowpos[kNextThreads / 32][kNextWarpTile];
+    uint32_t cls[2];
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const uint32_t per_day = (uint32_t)__popcll(mk[0][e] & ((1ULL << 60) - 1)) * (uint32_t)__popcll(mk[1][e] & ((1ULL << 60) - 1)) *
+                               (uint32_t)__popc((uint32_t)mk[2][e] & 0xFFFFFFu);
+      cls[e] = per_day > 24u ? 0u : (per_day > 1u ? 1u : 2u);
+    }
+    const uint32_t lt = (1u << lane) - 1u;
+    uint32_t base = 0, pos[2] = {0, 0};
+#pragma unroll
+    for (uint32_t c = 0; c < 3; ++c) {
+      const uint32_t b0 = __ballot_sync(0xffffffffu, cls[0] == c), b1 = __ballot_sync(0xffffffffu, cls[1] == c);
+      if (cls[0] == c) pos[0] = base + (uint32_t)__popc(b0 & lt);
+      if (cls[1] == c) pos[1] = base + (uint32_t)__popc(b0) + (uint32_t)__popc(b1 & lt);
+      base += (uint32_t)__popc(b0) + (uint32_t)__popc(b1);
+    }
+    uint64_t* xs = reinterpret_cast<uint64_t*>(stage);  // [64 rows][8 words]: 6 masks, from, zone
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int row = 2 * lane + e;
+      s_rowpos[warp][pos[e]] = (uint8_t)row;
+#pragma unroll
+      for (int p = 0; p < 6; ++p) xs[row * 8 + ((p + lane) & 7)] = mk[p][e];
+      xs[row * 8 + ((6 + lane) & 7)] = (uint64_t)fr[e];
+      xs[row * 8 + ((7 + lane) & 7)] = (uint64_t)(uint32_t)zz[e];
+    }
+    __syncwarp();
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      const int row = s_rowpos[warp][e * 32 + lane];
+      const int rl = row >> 1;
+      rows2[e] = row;
+#pragma unroll
+      for (int p = 0; p < 6; ++p) mk[p][e] = xs[row * 8 + ((p + rl) & 7)];
+      fr[e] = (int64_t)xs[row * 8 + ((6 + rl) & 7)];
+      zz[e] = (int32_t)(uint32_t)xs[row * 8 + ((7 + rl) & 7)];
+    }
+    __syncwarp();  // every lane holds its two specs in registers before the buffer starts taking results
+  }
+
   // The lane's two specs are walked one after the other through ONE copy of the walk in the instruction stream
   // (operands picked with selects): unrolling both into lock step doubled the code and spilled, and measured slower.
   Spec sp[2];
@@ -106,27 +159,27 @@ next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* 
   int64_t ra = kZero, rb = kZero;
 #pragma unroll 1
   for (int e = 0; e < 2; ++e) {
-    const bool live = i0 + e < n;  // out-of-range lanes stay in the loops (doing nothing) so the warp can re-sync
+    const int row = e ? rows2[1] : rows2[0];
+    const bool live = wbase + (size_t)row < n;  // out-of-range lanes stay in the loops (doing nothing) so the warp can re-sync
     const Spec ss = e ? sp[1] : sp[0];
     Walk w;
     int64_t t = e ? fr[1] : fr[0];
     bool ok = live && bind_checked(w, zt, e ? zz[1] : zz[0], t, err);
     if (!live) w.bind_utc();
     if (KT != 1 && !ss.never) w.tod_last = cronwalk::spec_tod_last(ss);  // lets chained calls skip exhausted days
-    const int row = 2 * lane + e;
 #pragma unroll 1
     for (int j = 0; j < kk; ++j) {
       // Every lane runs exactly kk iterations: re-converge here, otherwise lanes that took the short path of one
       // iteration run ahead and the warp executes each path of each iteration separately.
       __syncwarp();
       if (ok && t != kZero) {
-        t = cronwalk::next_from_t<B200CRON_NEXTN_OUTLINE != 0>(ss, w, t, j > 0);
+        t = cronwalk::next_from(ss, w, t, j > 0);
         // chained calls keep walking: re-check the zoned horizon (UTC never trips it)
         if (KT != 1 && t != kZero && w.zn > 1 && t >= zt.horizon - kSixYears) { atomicOr(err, kErrRange); ok = false; t = kZero; }
       } else {
         t = kZero;
       }
-      if (KT > 1) stage[row * KT + ((j + lane) & (KT - 1))] = t;
+      if (KT > 1) stage[row * KT + ((j + (row >> 1)) & (KT - 1))] = t;
       else if (KT == 0) stage[j * kNextWarpTile + row] = t;
     }
     if (e) rb = t; else ra = t;
@@ -166,10 +219,10 @@ next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* 
 // which measured as more than the 128-bit loads save.  Used when k == 1; next_n_kernel handles k > 1.
 // -------------------------------------------------------------------------------------------------------------
 #ifndef B200CRON_NEXT1_THREADS
-#define B200CRON_NEXT1_THREADS 64
+#define B200CRON_NEXT1_THREADS 128
 #endif
 #ifndef B200CRON_NEXT1_MINBLOCKS
-#define B200CRON_NEXT1_MINBLOCKS 16
+#define B200CRON_NEXT1_MINBLOCKS 12
 #endif
 constexpr int kNext1Threads = B200CRON_NEXT1_THREADS;
 
@@ -233,7 +286,7 @@ enum { kUnmetSingle = 0, kUnmetEasy = 1, kUnmetHard = 2 };
 #endif
 constexpr int kUnmetEasyRounds = B200CRON_UNMET_EASY_ROUNDS;
 #ifndef B200CRON_UNMET_EASY_MINBLOCKS
-#define B200CRON_UNMET_EASY_MINBLOCKS 12
+#define B200CRON_UNMET_EASY_MINBLOCKS 8
 #endif
 #ifndef B200CRON_UNMET_HARD_MINBLOCKS
 #define B200CRON_UNMET_HARD_MINBLOCKS 12
@@ -334,14 +387,14 @@ unmet_hard_kernel(UnmetArgs a, ZoneTable zt, int* __restrict__ err, const uint32
 // A CTA owns kHistSegs consecutive segments, i.e. one contiguous run of records.  The run's keys are brought into
 // shared memory with coalesced loads, every record finds its segment by binary search over the tile's offsets and
 // its stable rank by counting the records of its segment that sort before it (segments are short: the reference
-// keeps historyLimit of them), and perm/keep are staged in shared memory and written back coalesced.
+// keeps historyLimit of them), and perm/keep go straight to global memory (sector-coalesced, see below).
 // Runs longer than kHistCap records are ranked straight from global memory (L2-resident) -- correct for any
 // length, but quadratic in the segment length.
 // Algorithmic bytes: 8 (key) in, 4 (perm) + 1 (keep) out per record; 8 (offset) + 8 (limit) in per segment.
 // -------------------------------------------------------------------------------------------------------------
 constexpr int kHistThreads = 256;
 constexpr int kHistSegs = 256;
-constexpr int kHistCap = 3072;  // records per CTA tile held in shared memory (44 KB static with perm/keep/seg/offsets)
+constexpr int kHistCap = 3072;  // records per CTA tile held in shared memory (31 KB static with seg ids/offsets/limits)
 
 __global__ void __launch_bounds__(kHistThreads)
 history_prune_kernel(const uint64_t* __restrict__ seg_off, const int64_t* __restrict__ key,
@@ -349,8 +402,6 @@ history_prune_kernel(const uint64_t* __restrict__ seg_off, const int64_t* __rest
                      uint8_t* __restrict__ keep) {
   __shared__ uint64_t s_off[kHistSegs + 1];
   __shared__ int64_t s_key[kHistCap];
-  __shared__ uint32_t s_perm[kHistCap];
-  __shared__ uint8_t s_keep[kHistCap];
   const size_t seg0 = (size_t)blockIdx.x * kHistSegs;
   const int nsegs = (int)((nseg - seg0) < (size_t)kHistSegs ? (nseg - seg0) : (size_t)kHistSegs);
   for (int x = threadIdx.x; x <= nsegs; x += kHistThreads) s_off[x] = __ldg(seg_off + seg0 + x);
@@ -386,14 +437,12 @@ history_prune_kernel(const uint64_t* __restrict__ seg_off, const int64_t* __rest
         const int64_t kj = s_key[j];
         rank += (kj < kx) || (kj == kx && j < x);
       }
-      // sorted position `rank` is deleted when rank < len - limit
-      s_perm[a + rank] = x - a;
-      s_keep[a + rank] = !((int32_t)rank < (int32_t)(b - a) - s_lim[sg]);
-    }
-    __syncthreads();
-    for (uint32_t x = threadIdx.x; x < tot; x += kHistThreads) {
-      perm[r0 + x] = s_perm[x];
-      keep[r0 + x] = s_keep[x];
+      // sorted position `rank` is deleted when rank < len - limit.  Written straight to global memory: the lanes of a
+      // warp hold consecutive records, i.e. a handful of whole segments, and a permutation inside a segment touches
+      // the same 32-byte sectors as the identity would -- staging the outputs in shared memory bought nothing and
+      // cost 15 KB per CTA (4 resident CTAs per SM instead of 7).
+      perm[r0 + a + rank] = x - a;
+      keep[r0 + a + rank] = !((int32_t)rank < (int32_t)(b - a) - s_lim[sg]);
     }
     return;
   }

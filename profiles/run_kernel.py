@@ -17,6 +17,35 @@ torch.cuda.set_stream(stream)
 st = stream.cuda_stream
 t = lambda a: torch.from_numpy(a).cuda()  # noqa: E731
 ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+if which == "next1":
+    # the headline shape without bench.py's host-side set-up: 8 device-generated 1M-spec UTC batches, K back-to-back
+    # launches, overlap on and off (argv[3] = K)
+    K = int(sys.argv[3]) if len(sys.argv) > 3 else 200
+    nb, n1 = 8, 1_000_000
+    dm = [torch.empty((6, n1), dtype=torch.int64, device="cuda") for _ in range(nb)]
+    df = [torch.empty(n1, dtype=torch.int64, device="cuda") for _ in range(nb)]
+    do = [torch.empty((n1, 1), dtype=torch.int64, device="cuda") for _ in range(nb)]
+    for b in range(nb):
+        ctx.synth_specs_dev(dm[b], n1, 0xC0FFEE, b * n1, False, stream=st)
+        ctx.synth_times_dev(df[b], n1, synth.ts(2024), synth.ts(2034), 0xC0FFEE, b * n1, stream=st)
+    planes = [api._planes(x)[0] for x in dm]
+    L = api.lib()
+    for ov in (1, 0):
+        ctx.set_overlap(bool(ov))
+        best = 1e30
+        for rep in range(4):
+            for i in range(16):
+                L.b200cron_next_n_dev(ctx._h, 0, st, planes[i % nb], None, df[i % nb].data_ptr(), n1, 1, do[i % nb].data_ptr())
+            ctx.sync_check(stream=st)
+            ev0.record()
+            for i in range(K):
+                L.b200cron_next_n_dev(ctx._h, 0, st, planes[i % nb], None, df[i % nb].data_ptr(), n1, 1, do[i % nb].data_ptr())
+            ev1.record()
+            ctx.sync_check(stream=st)
+            best = min(best, ev0.elapsed_time(ev1) / K)
+        print("next1 overlap", ov, "us/step", best * 1e3, "roofline frac", 64e6 / (best * 1e-3) / 1e9 / 6555.5)
+    ctx.close()
+    sys.exit(0)
 if which == "unmet":
     m = synth.gen_specs(n, seed=41, dense_minutes=0.5)
     z = synth.gen_zone_ids(n, len(names), dst, seed=41)
