@@ -477,3 +477,65 @@ def test_unmet_zero_copy_on_pinned_buffers(ctx, names):
     got = ctx.unmet_since(hm.array, he.array, now, zone_id=hz.array, out=out)  # pinned: in place
     for k in KEYS:
         assert np.array_equal(got[k], want[k]), k
+
+
+def test_overlapping_independent_launches(ctx, names):
+    """b200cron_ctx_set_overlap: back-to-back k == 1 launches over independent batches may overlap on the GPU
+    (programmatic dependent launch); every batch must still get exactly the oracle's answers"""
+    import torch
+    nb, n = 6, 150_001
+    stream = torch.cuda.Stream()
+    st = stream.cuda_stream
+    masks = [synth.gen_specs(n, seed=70 + b) for b in range(nb)]
+    frm = [synth.gen_times(n, ts(2024), ts(2034), seed=70 + b) for b in range(nb)]
+    zid = [synth.gen_zone_ids(n, len(names), _dst_zones(ctx, names), seed=70 + b) if b % 2 else None for b in range(nb)]
+    with torch.cuda.stream(stream):
+        dm = [torch.from_numpy(m.view(np.int64)).cuda() for m in masks]
+        df = [torch.from_numpy(f).cuda() for f in frm]
+        dz = [None if z is None else torch.from_numpy(z).cuda() for z in zid]
+        out = [torch.full((n, 1), 7, dtype=torch.int64, device="cuda") for _ in range(nb)]
+    stream.synchronize()
+    ctx.set_overlap(True)
+    try:
+        for rep in range(3):
+            for b in range(nb):
+                ctx.next_n_dev(dm[b], df[b], out[b], 1, dz[b], stream=st)
+        ctx.sync_check(stream=st)
+    finally:
+        ctx.set_overlap(False)
+    for b in range(nb):
+        want = po.batch_next_n(masks[b], frm[b], 1, zid[b], names)
+        assert np.array_equal(out[b].cpu().numpy(), want), b
+
+
+def test_unmet_kernel_pair_on_concurrent_streams(ctx, names):
+    """the easy/hard unmet kernel pair hands Crons over through a small pool of scratch lists: calls on different
+    streams (more calls than lists, growing batch sizes) must not disturb each other"""
+    import torch
+    sizes = [3_001, 20_000, 777, 45_003, 12_345, 60_000, 5]
+    now = ts(2026, 3, 29, 12)
+    calls = []
+    for c, n in enumerate(sizes):
+        masks = synth.gen_specs(n, seed=90 + c, dense_minutes=0.5)
+        dense = np.array([bin(int(x) & ((1 << 60) - 1)).count("1") for x in masks[1]]) > 6
+        masks[2] = np.where(dense, masks[2] & np.uint64(0x800000000000000E), masks[2])  # affordable for the oracle
+        masks[2] = np.where(masks[2] & np.uint64(0xFFFFFF), masks[2], np.uint64(1 << 2))
+        zid = synth.gen_zone_ids(n, len(names), _dst_zones(ctx, names), seed=90 + c)
+        earliest = now - 30 * 86400 + synth.gen_times(n, -86400, 86400, seed=90 + c)
+        stream = torch.cuda.Stream()
+        with torch.cuda.stream(stream):
+            dm, dz, de = torch.from_numpy(masks.view(np.int64)).cuda(), torch.from_numpy(zid).cuda(), torch.from_numpy(earliest).cuda()
+            o = dict(last=torch.empty(n, dtype=torch.int64, device="cuda"), next=torch.empty(n, dtype=torch.int64, device="cuda"),
+                     missed=torch.empty(n, dtype=torch.int32, device="cuda"), status=torch.empty(n, dtype=torch.uint8, device="cuda"),
+                     decision=torch.empty(n, dtype=torch.uint8, device="cuda"))
+        calls.append((masks, zid, earliest, stream, dm, dz, de, o))
+    torch.cuda.synchronize()
+    for rep in range(2):
+        for masks, zid, earliest, stream, dm, dz, de, o in calls:
+            ctx.unmet_since_dev(dm, de, now, o, 0, None, None, None, None, dz, stream=stream.cuda_stream)
+    for _, _, _, stream, *_ in calls:
+        ctx.sync_check(stream=stream.cuda_stream)
+    for masks, zid, earliest, stream, dm, dz, de, o in calls:
+        want = po.batch_unmet(masks, earliest, now, zone_id=zid, zone_names=names)
+        got = {k: v.cpu().numpy().view(want[k].dtype) for k, v in o.items()}
+        _cmp(got, want, len(earliest))
