@@ -48,12 +48,6 @@ __device__ __forceinline__ bool bind_checked(Walk& w, const ZoneTable& zt, int32
 //   KT = 0 (any other k): transposed staging [j][row] and a division per element on the way out.
 // Algorithmic bytes: 48 (masks) + 8 (from) [+ 4 zone] in, 8k out per spec.
 // -------------------------------------------------------------------------------------------------------------
-#ifndef B200CRON_NEXTN_OUTLINE
-#define B200CRON_NEXTN_OUTLINE 0  // 1: the step emulation is called out of line (smaller loop body) -- tuning
-#endif
-#ifndef B200CRON_NEXTN_SORT
-#define B200CRON_NEXTN_SORT 1  // 0: walk the tile's specs in input order (tuning)
-#endif
 constexpr int kNextThreads = 64;
 constexpr int kNextWarpTile = 64;
 constexpr int kNextTile = kNextWarpTile * (kNextThreads / 32);
@@ -64,7 +58,6 @@ next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* 
               int64_t* __restrict__ out, ZoneTable zt, int* __restrict__ err) {
   extern __shared__ __align__(16) int64_t stage_all[];  // [warps][64 * k], unused when KT == 1
   const int k = KT > 0 ? KT : k_rt;
-  constexpr bool kSortTile = KT >= 8 && B200CRON_NEXTN_SORT != 0;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const size_t wbase = (size_t)blockIdx.x * kNextTile + (size_t)warp * kNextWarpTile;
   if (wbase >= n) return;
@@ -101,55 +94,6 @@ next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* 
     }
   }
 
-  // Divergence control for long chains (KT >= 8): the cost of one chained call depends on how often the spec fires --
-  // several times a day (next time of day on the resident day), once a day or less (next matching day), in between.
-  // A warp pays for every path any of its lanes takes, so the tile's 64 specs are dealt out by class: the warp's
-  // first pass walks the 32 that fire most often, the second pass the rest, and at most one pass mixes classes.
-  // The specs travel through the (still unused) output staging buffer; results are staged by original row, so the
-  // output order does not change.
-  int rows2[2] = {2 * lane, 2 * lane + 1};
-  if (kSortTile) {
-    __shared__ uint8_t s_rowpos[kNextThreads / 32][kNextWarpTile];
-    uint32_t cls[2];
-#pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      const uint32_t per_day = (uint32_t)__popcll(mk[0][e] & ((1ULL << 60) - 1)) * (uint32_t)__popcll(mk[1][e] & ((1ULL << 60) - 1)) *
-                               (uint32_t)__popc((uint32_t)mk[2][e] & 0xFFFFFFu);
-      cls[e] = per_day > 24u ? 0u : (per_day > 1u ? 1u : 2u);
-    }
-    const uint32_t lt = (1u << lane) - 1u;
-    uint32_t base = 0, pos[2] = {0, 0};
-#pragma unroll
-    for (uint32_t c = 0; c < 3; ++c) {
-      const uint32_t b0 = __ballot_sync(0xffffffffu, cls[0] == c), b1 = __ballot_sync(0xffffffffu, cls[1] == c);
-      if (cls[0] == c) pos[0] = base + (uint32_t)__popc(b0 & lt);
-      if (cls[1] == c) pos[1] = base + (uint32_t)__popc(b0) + (uint32_t)__popc(b1 & lt);
-      base += (uint32_t)__popc(b0) + (uint32_t)__popc(b1);
-    }
-    uint64_t* xs = reinterpret_cast<uint64_t*>(stage);  // [64 rows][8 words]: 6 masks, from, zone
-#pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      const int row = 2 * lane + e;
-      s_rowpos[warp][pos[e]] = (uint8_t)row;
-#pragma unroll
-      for (int p = 0; p < 6; ++p) xs[row * 8 + ((p + lane) & 7)] = mk[p][e];
-      xs[row * 8 + ((6 + lane) & 7)] = (uint64_t)fr[e];
-      xs[row * 8 + ((7 + lane) & 7)] = (uint64_t)(uint32_t)zz[e];
-    }
-    __syncwarp();
-#pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      const int row = s_rowpos[warp][e * 32 + lane];
-      const int rl = row >> 1;
-      rows2[e] = row;
-#pragma unroll
-      for (int p = 0; p < 6; ++p) mk[p][e] = xs[row * 8 + ((p + rl) & 7)];
-      fr[e] = (int64_t)xs[row * 8 + ((6 + rl) & 7)];
-      zz[e] = (int32_t)(uint32_t)xs[row * 8 + ((7 + rl) & 7)];
-    }
-    __syncwarp();  // every lane holds its two specs in registers before the buffer starts taking results
-  }
-
   // The lane's two specs are walked one after the other through ONE copy of the walk in the instruction stream
   // (operands picked with selects): unrolling both into lock step doubled the code and spilled, and measured slower.
   Spec sp[2];
@@ -159,8 +103,8 @@ next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* 
   int64_t ra = kZero, rb = kZero;
 #pragma unroll 1
   for (int e = 0; e < 2; ++e) {
-    const int row = e ? rows2[1] : rows2[0];
-    const bool live = wbase + (size_t)row < n;  // out-of-range lanes stay in the loops (doing nothing) so the warp can re-sync
+    const int row = 2 * lane + e;
+    const bool live = i0 + e < n;  // out-of-range lanes stay in the loops (doing nothing) so the warp can re-sync
     const Spec ss = e ? sp[1] : sp[0];
     Walk w;
     int64_t t = e ? fr[1] : fr[0];
@@ -179,7 +123,7 @@ next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* 
       } else {
         t = kZero;
       }
-      if (KT > 1) stage[row * KT + ((j + (row >> 1)) & (KT - 1))] = t;
+      if (KT > 1) stage[row * KT + ((j + lane) & (KT - 1))] = t;
       else if (KT == 0) stage[j * kNextWarpTile + row] = t;
     }
     if (e) rb = t; else ra = t;
@@ -222,7 +166,7 @@ next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* 
 #define B200CRON_NEXT1_THREADS 128
 #endif
 #ifndef B200CRON_NEXT1_MINBLOCKS
-#define B200CRON_NEXT1_MINBLOCKS 12
+#define B200CRON_NEXT1_MINBLOCKS 16
 #endif
 constexpr int kNext1Threads = B200CRON_NEXT1_THREADS;
 
@@ -277,12 +221,12 @@ struct UnmetArgs {
 // only the closed form answer, gives every Cron at most kUnmetEasyRounds rounds (first fire + fast-forward, end of
 // chain, Next(now)) and appends the Crons that need more -- a zone transition in the way, a step only the emulation
 // can take -- to a compact index list; the hard kernel then runs the general state machine over that list only, in
-// dense warps.  On the C4 workload 8 % of the Crons are deferred (all zoned; 2.4 % need the step emulation, which in
+// dense warps.  On the C4 workload 4.6 % of the Crons are deferred (all zoned; 2.4 % need the step emulation, which in
 // the single kernel made every second warp run it for one or two lanes).  The easy kernel has no step emulation in
 // its instruction stream and its lanes stay together.
 enum { kUnmetSingle = 0, kUnmetEasy = 1, kUnmetHard = 2 };
 #ifndef B200CRON_UNMET_EASY_ROUNDS
-#define B200CRON_UNMET_EASY_ROUNDS 3
+#define B200CRON_UNMET_EASY_ROUNDS 4
 #endif
 constexpr int kUnmetEasyRounds = B200CRON_UNMET_EASY_ROUNDS;
 #ifndef B200CRON_UNMET_EASY_MINBLOCKS
