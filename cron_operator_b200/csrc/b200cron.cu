@@ -138,7 +138,7 @@ cudaError_t launch_next(b200cron_ctx* ctx, const Device& d, cudaStream_t st, con
   bool vec = aligned16(from) && aligned16(out) && (!zone || (reinterpret_cast<uintptr_t>(zone) & 7u) == 0);
   for (int p = 0; p < 6; ++p) vec = vec && (m.p[p] == nullptr || aligned16(m.p[p]));
   const unsigned grid = (unsigned)((n + kNextTile - 1) / kNextTile);
-  const size_t smem = k == 1 ? 0 : (size_t)kNextTile * k * sizeof(int64_t);
+  const size_t smem = (k == 1 || !kNextStage) ? 0 : (size_t)kNextTile * k * sizeof(int64_t);
   ctx->launches.fetch_add(1, std::memory_order_relaxed);
   if (k == 1 && !getenv("B200CRON_NEXT1_PAIRED")) {  // one spec per lane (finer waves); the env var selects the paired kernel
     const unsigned g1 = (unsigned)((n + kNext1Threads - 1) / kNext1Threads);

@@ -48,12 +48,19 @@ __device__ __forceinline__ bool bind_checked(Walk& w, const ZoneTable& zt, int32
 //   KT = 0 (any other k): transposed staging [j][row] and a division per element on the way out.
 // Algorithmic bytes: 48 (masks) + 8 (from) [+ 4 zone] in, 8k out per spec.
 // -------------------------------------------------------------------------------------------------------------
+#ifndef B200CRON_NEXTN_STAGE
+#define B200CRON_NEXTN_STAGE 1  // 0: results go straight to global memory, no shared-memory staging (tuning)
+#endif
+#ifndef B200CRON_NEXTN_MINBLOCKS
+#define B200CRON_NEXTN_MINBLOCKS 12
+#endif
+constexpr bool kNextStage = B200CRON_NEXTN_STAGE != 0;
 constexpr int kNextThreads = 64;
 constexpr int kNextWarpTile = 64;
 constexpr int kNextTile = kNextWarpTile * (kNextThreads / 32);
 
 template <int KT, bool kVec>
-__global__ void __launch_bounds__(kNextThreads, 12)
+__global__ void __launch_bounds__(kNextThreads, B200CRON_NEXTN_MINBLOCKS)
 next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* __restrict__ from, size_t n, int k_rt,
               int64_t* __restrict__ out, ZoneTable zt, int* __restrict__ err) {
   extern __shared__ __align__(16) int64_t stage_all[];  // [warps][64 * k], unused when KT == 1
@@ -123,7 +130,8 @@ next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* 
       } else {
         t = kZero;
       }
-      if (KT > 1) stage[row * KT + ((j + lane) & (KT - 1))] = t;
+      if (!kNextStage) { if (KT != 1 && live) out[(i0 + e) * (size_t)k + j] = t; }
+      else if (KT > 1) stage[row * KT + ((j + lane) & (KT - 1))] = t;
       else if (KT == 0) stage[j * kNextWarpTile + row] = t;
     }
     if (e) rb = t; else ra = t;
@@ -138,6 +146,7 @@ next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* 
     }
     return;
   }
+  if (!kNextStage) return;
   __syncwarp();
   const int rows = (int)((n - wbase) < (size_t)kNextWarpTile ? (n - wbase) : (size_t)kNextWarpTile);
   int64_t* dst = out + wbase * (size_t)k;

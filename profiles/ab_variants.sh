@@ -6,7 +6,7 @@ for v in "" $(ls $V/lib_[eh]*.so 2>/dev/null); do
   echo "== unmet ${v:-default}"
   B200CRON_LIB=$v python profiles/run_kernel.py unmet 10000000 5
 done
-for v in "" $(ls $V/lib_n*.so 2>/dev/null); do
+for v in $(ls $V/lib_n*.so 2>/dev/null); do
   echo "== next1 ${v:-default}"
   B200CRON_LIB=$v python profiles/run_kernel.py next1 1000000 200
 done
@@ -14,5 +14,7 @@ for v in "" $(ls $V/lib_o*.so 2>/dev/null); do
   echo "== nextn ${v:-default}"
   B200CRON_LIB=$v python profiles/run_kernel.py nextn 8000000 5
 done
-echo "== history default"
-python profiles/run_kernel.py history 8000000 5
+if [ -n "$AB_HISTORY" ]; then
+  echo "== history default"
+  python profiles/run_kernel.py history 8000000 5
+fi

@@ -85,5 +85,8 @@ for _ in range(reps):
     ev1.record()
     ctx.sync_check(stream=st)
     best = min(best, ev0.elapsed_time(ev1))
-print(which, n, "ms", best)
+extra = ""
+if which == "nextn":  # variants must agree: a cheap fingerprint of the whole output
+    extra = " checksum %d" % int((o ^ (o >> 17)).sum().item())
+print(which, n, "ms", best, extra)
 ctx.close()
