@@ -34,7 +34,7 @@ from cron_operator_b200 import synth  # noqa: E402
 N_SPECS = 1_000_000          # C2
 BYTES_PER_EVAL = 64          # 48 masks + 8 from + 8 out
 T_LO, T_HI = synth.ts(2024), synth.ts(2034)
-NCU_TRAFFIC_BYTES = 56_067_072 + 359_424  # one launch of next1_kernel, profiles/r1e_ncu_next1_summary.md
+NCU_TRAFFIC_BYTES = 56_009_216 + 386_560  # one launch of next1_kernel, profiles/r1h_ncu_next1_summary.md
 METRIC = "schedule_evals_per_sec"
 UNIT = "evals/s"
 WORKLOAD = "C2: 1M random 5-field UTC cron specs, next single fire time (per GPU)"
@@ -350,7 +350,7 @@ def main():
                            "place over PCIe (seconds plane NULL = second 0, as ParseStandard always yields)"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": NCU_TRAFFIC_BYTES, "traffic_source": "profiles/r1e_ncu_next1_summary.md "
+                         "traffic": NCU_TRAFFIC_BYTES, "traffic_source": "profiles/r1h_ncu_next1_summary.md "
                          "(dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full; the 8 MB output "
                          "is still largely in L2 when the kernel ends)",
                          "peak_source": peak_src, "kernel": "next1_kernel",

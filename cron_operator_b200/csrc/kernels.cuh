@@ -227,15 +227,16 @@ struct UnmetArgs {
 // code (ncu: 21 % issue-active at 24 warps/SM); more resident warps hide them -- measured 8.3 -> 6.9 ms per 10M Crons.
 //
 // Modes.  kUnmetSingle: one launch does everything.  kUnmetEasy + kUnmetHard (the default pair): the easy kernel lets
-// only the closed form answer, gives every Cron at most kUnmetEasyRounds rounds (first fire + fast-forward, end of
-// chain, Next(now)) and appends the Crons that need more -- a zone transition in the way, a step only the emulation
-// can take -- to a compact index list; the hard kernel then runs the general state machine over that list only, in
-// dense warps.  On the C4 workload 4.6 % of the Crons are deferred (all zoned; 2.4 % need the step emulation, which in
-// the single kernel made every second warp run it for one or two lanes).  The easy kernel has no step emulation in
-// its instruction stream and its lanes stay together.
+// only the closed form answer, gives every Cron at most kUnmetEasyRounds rounds (first fire + fast-forward, a zone
+// transition crossed + fast-forward, ..., end of chain, Next(now)) and appends the Crons that need more -- a step only
+// the emulation can take, a backward step -- to a compact index list; the hard kernel then runs the general state
+// machine over that list only, in dense warps.  On the C4 workload (10M Crons, B200) 3 rounds defer 8 % of the Crons
+// and take 5.23 ms, 4 rounds 4.6 % / 4.79 ms, 5 rounds 2.4 % / 4.34 ms, 6 rounds the same 2.4 % / 4.35 ms: what is
+// left after five rounds needs the step emulation, which in the single kernel (7.30 ms) made every second warp run it
+// for one or two lanes.  The easy kernel has no step emulation in its instruction stream.
 enum { kUnmetSingle = 0, kUnmetEasy = 1, kUnmetHard = 2 };
 #ifndef B200CRON_UNMET_EASY_ROUNDS
-#define B200CRON_UNMET_EASY_ROUNDS 4
+#define B200CRON_UNMET_EASY_ROUNDS 5
 #endif
 constexpr int kUnmetEasyRounds = B200CRON_UNMET_EASY_ROUNDS;
 #ifndef B200CRON_UNMET_EASY_MINBLOCKS
