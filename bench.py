@@ -294,6 +294,18 @@ def main():
     launches = ctx.launch_count - launches0
     ctx.sync_check(stream=st)
     dev_s = e0.elapsed_time(e1) * 1e-3
+    # for the record: the same K steps with every launch waiting for the previous one to finish (overlap off)
+    serial_ms = None
+    if not args.no_overlap:
+        ctx.set_overlap(False)
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record()
+        for i in range(args.steps):
+            step(i % N_BATCH)
+        s1.record()
+        ctx.sync_check(stream=st)
+        serial_ms = s0.elapsed_time(s1) / args.steps
+        ctx.set_overlap(True)
     # cross-check: the same kernel timed one launch at a time with the L2 flushed before each (includes launch latency)
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(min(args.steps, 30))]
     for i, (a, b) in enumerate(ev):
@@ -355,6 +367,7 @@ def main():
                          "is still largely in L2 when the kernel ends)",
                          "peak_source": peak_src, "kernel": "next1_kernel",
                          "algorithmic_bytes_per_launch": BYTES_PER_EVAL * N_SPECS,
+                         "ms_per_step_overlap_off": serial_ms,
                          "flushed_single_launch_ms_min_med_max": [min(kernel_ms), float(np.median(kernel_ms)), max(kernel_ms)],
                          "note": "cross-check: one launch at a time after a 256 MiB L2 flush, includes launch latency"},
             "clocks": clocks,
