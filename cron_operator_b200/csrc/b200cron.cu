@@ -44,6 +44,10 @@ struct DeferList {
   uint32_t* count = nullptr;
   size_t cap = 0;  // entries
   cudaEvent_t done = nullptr;
+  // opt-in zone order (B200CRON_UNMET_ZONE_ORDER=1): Cron indices grouped by zone id, and 2 x nzones counters
+  uint32_t* order = nullptr;
+  size_t order_cap = 0;
+  uint32_t* zone_counts = nullptr;
 };
 constexpr int kDeferLists = 3;
 
@@ -194,8 +198,34 @@ cudaError_t launch_unmet(b200cron_ctx* ctx, Device& d, cudaStream_t st, const Un
     b.cap = a.n;
   }
   if ((e = cudaMemsetAsync(b.count, 0, sizeof(uint32_t), st)) != cudaSuccess) return e;
-  ctx->launches.fetch_add(2, std::memory_order_relaxed);
-  unmet_kernel<kUnmetEasy><<<grid, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, b.idx, b.count);
+  static const bool zone_order = getenv("B200CRON_UNMET_ZONE_ORDER") != nullptr;  // opt-in, see kernels.cuh
+  if (zone_order && a.zone_id) {
+    const int32_t nz = d.zt.nzones;
+    if (!b.zone_counts && (e = cudaMalloc(&b.zone_counts, 2 * (size_t)nz * sizeof(uint32_t))) != cudaSuccess) return e;
+    if (a.n > b.order_cap) {
+      if (b.order) {
+        if ((e = cudaEventSynchronize(b.done)) != cudaSuccess) return e;
+        if ((e = cudaFree(b.order)) != cudaSuccess) return e;
+        b.order = nullptr;
+        b.order_cap = 0;
+      }
+      if ((e = cudaMalloc(&b.order, a.n * sizeof(uint32_t))) != cudaSuccess) return e;
+      b.order_cap = a.n;
+    }
+    uint32_t* hist = b.zone_counts;
+    uint32_t* cursor = b.zone_counts + nz;
+    if ((e = cudaMemsetAsync(hist, 0, (size_t)nz * sizeof(uint32_t), st)) != cudaSuccess) return e;
+    const unsigned zgrid = (unsigned)((a.n + kZoneOrderTile - 1) / kZoneOrderTile);
+    ctx->launches.fetch_add(5, std::memory_order_relaxed);
+    zone_order_hist_kernel<<<zgrid, kZoneOrderThreads, (size_t)nz * sizeof(uint32_t), st>>>(a.zone_id, a.n, nz, hist);
+    zone_order_scan_kernel<<<1, kZoneOrderThreads, 0, st>>>(hist, nz, cursor);
+    zone_order_scatter_kernel<<<zgrid, kZoneOrderThreads, 2 * (size_t)nz * sizeof(uint32_t), st>>>(a.zone_id, a.n, nz,
+                                                                                                  cursor, b.order);
+    unmet_kernel<kUnmetEasy, true><<<grid, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, b.idx, b.count, b.order);
+  } else {
+    ctx->launches.fetch_add(2, std::memory_order_relaxed);
+    unmet_kernel<kUnmetEasy><<<grid, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, b.idx, b.count);
+  }
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
   const unsigned hard_grid = grid < 148u * 12u ? grid : 148u * 12u;
   unmet_hard_kernel<<<hard_grid, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, b.idx, b.count);
@@ -343,6 +373,8 @@ extern "C" void b200cron_ctx_destroy(b200cron_ctx* ctx) {
     for (DeferList& b : d.defer) {
       if (b.idx) cudaFree(b.idx);
       if (b.count) cudaFree(b.count);
+      if (b.order) cudaFree(b.order);
+      if (b.zone_counts) cudaFree(b.zone_counts);
       if (b.done) cudaEventDestroy(b.done);
     }
     if (d.h_err) cudaFreeHost(d.h_err);

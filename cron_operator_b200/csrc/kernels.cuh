@@ -313,12 +313,15 @@ __device__ __forceinline__ void unmet_one(const UnmetArgs& a, const ZoneTable& z
   }
 }
 
-template <int kMode>
+// kOrdered: the launch walks the Crons in the order of an index list (zone_order_* kernels below) instead of input order
+template <int kMode, bool kOrdered = false>
 __global__ void __launch_bounds__(kUnmetThreads, kMode == kUnmetEasy ? B200CRON_UNMET_EASY_MINBLOCKS : 12)
 unmet_kernel(UnmetArgs a, ZoneTable zt, int* __restrict__ err, uint32_t* __restrict__ defer_idx,
-             uint32_t* __restrict__ defer_count) {
-  const size_t i = (size_t)blockIdx.x * kUnmetThreads + threadIdx.x;
-  unmet_one<kMode>(a, zt, err, i, i < a.n, defer_idx, defer_count);
+             uint32_t* __restrict__ defer_count, const uint32_t* __restrict__ order = nullptr) {
+  const size_t q = (size_t)blockIdx.x * kUnmetThreads + threadIdx.x;
+  const bool live = q < a.n;
+  const size_t i = kOrdered ? (live ? (size_t)__ldg(order + q) : 0) : q;
+  unmet_one<kMode>(a, zt, err, i, live, defer_idx, defer_count);
 }
 
 // the general state machine over the compact list the easy kernel left behind (grid-stride: the host does not know
@@ -331,6 +334,89 @@ unmet_hard_kernel(UnmetArgs a, ZoneTable zt, int* __restrict__ err, const uint32
     const size_t q = base + threadIdx.x;
     const bool live = q < cnt;
     unmet_one<kUnmetHard>(a, zt, err, live ? defer_idx[q] : 0, live, nullptr, nullptr);
+  }
+}
+
+// -------------------------------------------------------------------------------------------------------------
+// Zone order (opt-in, B200CRON_UNMET_ZONE_ORDER=1; written at the end of round 1 and NOT yet run on a GPU -- see
+// DESIGN.md section 8).  The easy kernel spends its time in zone-dependent code that 4-5 of a warp's 32 lanes execute
+// together: half of the lanes are UTC and the zoned ones sit in different zones, hence in different periods.  A
+// counting sort of the Cron indices by zone id (histogram, scan, scatter; one pass over zone_id each) lets the easy
+// kernel walk zone-pure warps through an index list; inputs are then gathered and outputs scattered 8 bytes at a
+// time, which is cheap next to the divergence it removes.  Ids outside [0, nzones) are binned with UTC; unmet_one
+// reports them as before.
+// -------------------------------------------------------------------------------------------------------------
+constexpr int kZoneOrderThreads = 256;
+constexpr int kZoneOrderItems = 16;  // Crons per thread: a CTA bins 4096 consecutive Crons
+constexpr int kZoneOrderTile = kZoneOrderThreads * kZoneOrderItems;
+
+__device__ __forceinline__ uint32_t zone_bin(const int32_t* __restrict__ zone_id, size_t i, int32_t nzones) {
+  const int32_t z = __ldg(zone_id + i);
+  return (z < 0 || z >= nzones) ? 0u : (uint32_t)z;
+}
+
+// the CTA's histogram of its tile in shared memory (bins [0, nzones)); all threads call it
+__device__ __forceinline__ void zone_tile_hist(const int32_t* __restrict__ zone_id, size_t n, int32_t nzones,
+                                               uint32_t* __restrict__ sh) {
+  for (int b = threadIdx.x; b < nzones; b += kZoneOrderThreads) sh[b] = 0;
+  __syncthreads();
+  const size_t base = (size_t)blockIdx.x * kZoneOrderTile;
+#pragma unroll 4
+  for (int it = 0; it < kZoneOrderItems; ++it) {
+    const size_t i = base + (size_t)it * kZoneOrderThreads + threadIdx.x;
+    if (i < n) atomicAdd(&sh[zone_bin(zone_id, i, nzones)], 1u);
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(kZoneOrderThreads)
+zone_order_hist_kernel(const int32_t* __restrict__ zone_id, size_t n, int32_t nzones, uint32_t* __restrict__ hist) {
+  extern __shared__ uint32_t zo_sh[];
+  zone_tile_hist(zone_id, n, nzones, zo_sh);
+  for (int b = threadIdx.x; b < nzones; b += kZoneOrderThreads)
+    if (zo_sh[b]) atomicAdd(hist + b, zo_sh[b]);
+}
+
+// exclusive prefix sum of the histogram into `cursor` (one CTA; a thread owns a contiguous run of bins)
+__global__ void __launch_bounds__(kZoneOrderThreads)
+zone_order_scan_kernel(const uint32_t* __restrict__ hist, int32_t nzones, uint32_t* __restrict__ cursor) {
+  __shared__ uint32_t part[kZoneOrderThreads];
+  const int per = (nzones + kZoneOrderThreads - 1) / kZoneOrderThreads;
+  const int lo = threadIdx.x * per, hi = min(lo + per, (int)nzones);
+  uint32_t sum = 0;
+  for (int b = lo; b < hi; ++b) sum += hist[b];
+  part[threadIdx.x] = sum;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t run = 0;
+    for (int t = 0; t < kZoneOrderThreads; ++t) { const uint32_t v = part[t]; part[t] = run; run += v; }
+  }
+  __syncthreads();
+  uint32_t run = part[threadIdx.x];
+  for (int b = lo; b < hi; ++b) { cursor[b] = run; run += hist[b]; }
+}
+
+// every CTA reserves, per zone, a range of the output for its tile's Crons and fills it
+__global__ void __launch_bounds__(kZoneOrderThreads)
+zone_order_scatter_kernel(const int32_t* __restrict__ zone_id, size_t n, int32_t nzones, uint32_t* __restrict__ cursor,
+                          uint32_t* __restrict__ order) {
+  extern __shared__ uint32_t zo_sh[];  // [nzones] counts, then local cursors; [nzones] bases
+  uint32_t* sh_base = zo_sh + nzones;
+  zone_tile_hist(zone_id, n, nzones, zo_sh);
+  for (int b = threadIdx.x; b < nzones; b += kZoneOrderThreads) {
+    const uint32_t c = zo_sh[b];
+    sh_base[b] = c ? atomicAdd(cursor + b, c) : 0u;
+    zo_sh[b] = 0;
+  }
+  __syncthreads();
+  const size_t base = (size_t)blockIdx.x * kZoneOrderTile;
+#pragma unroll 4
+  for (int it = 0; it < kZoneOrderItems; ++it) {
+    const size_t i = base + (size_t)it * kZoneOrderThreads + threadIdx.x;
+    if (i < n) {
+      const uint32_t b = zone_bin(zone_id, i, nzones);
+      order[sh_base[b] + atomicAdd(&zo_sh[b], 1u)] = (uint32_t)i;
+    }
   }
 }
 

@@ -6,6 +6,10 @@ for v in "" $(ls $V/lib_[eh]*.so 2>/dev/null); do
   echo "== unmet ${v:-default}"
   B200CRON_LIB=$v python profiles/run_kernel.py unmet 10000000 5
 done
+echo "== unmet default, zone order (opt-in, same checksum expected)"
+B200CRON_UNMET_ZONE_ORDER=1 python profiles/run_kernel.py unmet 10000000 5
+echo "== unmet single kernel"
+B200CRON_UNMET_SINGLE=1 python profiles/run_kernel.py unmet 10000000 5
 for v in $(ls $V/lib_n*.so 2>/dev/null); do
   echo "== next1 ${v:-default}"
   B200CRON_LIB=$v python profiles/run_kernel.py next1 1000000 200

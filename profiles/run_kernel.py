@@ -88,5 +88,7 @@ for _ in range(reps):
 extra = ""
 if which == "nextn":  # variants must agree: a cheap fingerprint of the whole output
     extra = " checksum %d" % int((o ^ (o >> 17)).sum().item())
+if which == "unmet":
+    extra = " checksum %d" % int(sum((v.to(torch.int64) * (j + 3)).sum().item() for j, v in enumerate(o.values())) & (2**63 - 1))
 print(which, n, "ms", best, extra)
 ctx.close()
