@@ -72,6 +72,19 @@ def main(rounds):
                 b = bad[0]
                 print("MISMATCH unmet", key, NAMES[zz[b]], int(e[b]), now, [hex(int(x)) for x in m2[:, b]], g[key][b], w[key][b])
                 return 1
+        # the kernels' easy/hard split (unmet_kernel<easy> + unmet_hard_kernel) over the full-density masks: the general
+        # machine (pinned to the oracle just above on the thinned masks) is the reference here
+        for er in (2, 5):
+            full = np.ascontiguousarray(masks[:, :20000])
+            e2 = near_transition_times(rng, zid[:20000], now - 20 * 86400, now, 86400 * 3)
+            g1 = shim.unmet(full, e2, now, zone_id=zid[:20000])
+            g2 = shim.unmet_two_phase(full, e2, now, er, zone_id=zid[:20000])
+            for key in ("last", "next", "missed", "status", "decision"):
+                bad = np.nonzero(g1[key] != g2[key])[0]
+                if len(bad):
+                    b = bad[0]
+                    print("MISMATCH two-phase", er, key, NAMES[zid[b]], int(e2[b]), now, [hex(int(x)) for x in full[:, b]])
+                    return 1
         print(f"round {r}: ok ({tot} evals, {time.time() - t0:.0f}s)", flush=True)
     return 0
 
