@@ -29,6 +29,17 @@
 #define CW_LDG(p) (*(p))
 #endif
 
+#ifndef B200CRON_WALK_DAY_PLAIN
+// 1: chained calls that stay on a day lying wholly inside one zone period skip the closed form's prerequisites (see
+// Walk::day_plain).  Opt-in: verified against the oracle on the host build, not yet timed on a GPU.
+#define B200CRON_WALK_DAY_PLAIN 0
+#endif
+#if B200CRON_WALK_DAY_PLAIN
+#define CW_DAY_PLAIN(stmt) stmt
+#else
+#define CW_DAY_PLAIN(stmt)
+#endif
+
 #ifndef CW_TRACE
 #define CW_TRACE(tag, w)
 #endif
@@ -205,6 +216,11 @@ struct Walk {
   int32_t sod;  // local second of day
   int32_t Y, M, D;
   bool today_ok;  // the resident day is known to satisfy the month and day masks (set when a fire was found on it)
+#if B200CRON_WALK_DAY_PLAIN
+  // today_ok, and the resident local day is natural from end to end and ends inside the cached period (whole-minute
+  // offset): every later fire of this day is then "next matching time of day", with nothing else to check
+  bool day_plain;
+#endif
   // chained calls (NextN): day mask of the resident month, and the day's last matching second (86400 = not set)
   uint32_t dm_month;
   bool dm_ok;
@@ -217,12 +233,14 @@ struct Walk {
   }
   CW_HD void bind_utc() {
     zw = nullptr; zo = nullptr; zf = nullptr; zn = 1; pidx = 0; off = 0; ps = kAlpha; pe = kOmega; nlo = kAlpha; nhi = kOmega; today_ok = false; dm_ok = false; dm_month = 0; tod_last = 86400;
+    CW_DAY_PLAIN(day_plain = false;)
   }
   CW_HD void bind_zone(const ZoneTable& zt, int32_t zone) {
     const int32_t a = CW_LDG(zt.zstart + zone), b = CW_LDG(zt.zstart + zone + 1);
     zw = zt.when + a; zo = zt.off + a; zf = zt.fpre + a; zn = b - a;
     pidx = -1; off = 0; ps = 1; pe = 0; nlo = 1; nhi = 0;  // empty cache
     today_ok = false; dm_ok = false; dm_month = 0; tod_last = 86400;
+    CW_DAY_PLAIN(day_plain = false;)
     if (zn == 1) { pidx = 0; off = CW_LDG(zo); ps = kAlpha; pe = kOmega; nlo = kAlpha; nhi = kOmega; }
   }
 
@@ -239,6 +257,7 @@ struct Walk {
       if (x < CW_LDG(zw + mid)) hi = mid; else lo = mid;
     }
     pidx = lo;
+    CW_DAY_PLAIN(day_plain = false;)
     off = CW_LDG(zo + lo);
     ps = CW_LDG(zw + lo);
     pe = (lo + 1 < zn) ? CW_LDG(zw + lo + 1) : kOmega;
@@ -264,9 +283,17 @@ struct Walk {
     sod = r * 128 + (int32_t)(l & 127);
     civil_from_days(dn, Y, M, D);
     today_ok = false;
+    CW_DAY_PLAIN(day_plain = false;)
     dm_ok = false;
   }
 
+#if B200CRON_WALK_DAY_PLAIN
+  // call with the walk on a fire time whose day matched (today_ok) and the period cache on that fire
+  CW_HD void mark_day_plain() {
+    day_plain = (off % 60 == 0) && t >= ps && nlo <= (int64_t)dn * 86400 && (int64_t)(dn + 1) * 86400 <= nhi &&
+                (pe == kOmega || t + (86400 - sod) <= pe);
+  }
+#endif
   // load() for a walk bound to UTC: no period lookup
   CW_HD void load_utc(int64_t tt) {
     t = tt;
@@ -278,6 +305,7 @@ struct Walk {
     sod = r * 128 + (int32_t)(tt & 127);
     civil_from_days(dn, Y, M, D);
     today_ok = false;
+    CW_DAY_PLAIN(day_plain = false;)
     dm_ok = false;
   }
 
@@ -318,6 +346,7 @@ struct Walk {
   // move the resident fields forward by k whole days inside the same period (k >= 1, small)
   CW_HD void advance_days(int32_t k) {
     today_ok = false;
+    CW_DAY_PLAIN(day_plain = false;)
     dm_ok = false;
     dn += k;
     D += k;
@@ -616,6 +645,7 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
       if (kUtcOnly || (w.t + (86400 - sod) < w.pe && w.natural(x1) && w.natural(xk) && r < w.pe)) {
         w.t = r;
         w.dn += k; w.D = Dn; w.sod = s.tod1;
+        CW_DAY_PLAIN(w.mark_day_plain();)
         *out = r;
         return true;
       }
@@ -646,6 +676,7 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
         w.t = r;
         w.sod = rsod;
         w.today_ok = true;
+        CW_DAY_PLAIN(w.mark_day_plain();)
         if (have_dm) { w.dm_month = dm; w.dm_ok = true; }
         *out = r;
         return true;
@@ -702,6 +733,7 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
     w.t = x_mid + s.tod1 - (kUtcOnly ? 0 : w.off);
     w.dn = found_dn; w.sod = s.tod1; w.Y = Yc; w.M = Mc; w.D = Dc;
     w.today_ok = true;
+    CW_DAY_PLAIN(w.mark_day_plain();)
     w.dm_month = dm_found; w.dm_ok = true;
     *out = w.t;
     return true;
@@ -736,6 +768,7 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
   w.t = r;
   w.dn = found_dn; w.sod = rsod; w.Y = Yc; w.M = Mc; w.D = Dc;
   w.today_ok = true;
+  CW_DAY_PLAIN(w.mark_day_plain();)
   w.dm_month = dm_found; w.dm_ok = true;
   *out = r;
   return true;
@@ -748,6 +781,17 @@ template <bool kUtcOnly = false>
 CW_HD bool next_try(const Spec& s, Walk& w, int64_t t, bool resident, int64_t* out) {
   CW_COUNT(next);
   if (s.never) { *out = kZero; return true; }
+#if B200CRON_WALK_DAY_PLAIN
+  if (resident && w.day_plain && w.sod + 1 < 86400) {
+    const int32_t tod = next_tod_ge(s, w.sod + 1);
+    if (tod >= 0) {
+      w.t += tod - w.sod;
+      w.sod = tod;
+      *out = w.t;
+      return true;
+    }
+  }
+#endif
   const int64_t t1 = t + 1;
   if (resident && (kUtcOnly || t1 < w.pe) && w.sod + 1 < 86400) {
     w.t = t1;
@@ -777,6 +821,7 @@ SlowResult walk_next_outlined(Spec s, Walk w) {
   x.w.lookup(x.w.t);  // fast_next may have moved the period cache; the step emulation wants it on t
   x.r = walk_next(s, x.w);
   x.w.today_ok = false;  // the emulation can end on a day upstream never re-checked
+  CW_DAY_PLAIN(x.w.day_plain = false;)
   x.w.dm_ok = false;
   return x;
 }
@@ -793,6 +838,7 @@ CW_HD int64_t next_slow(const Spec& s, Walk& w) {
   w.lookup(w.t);
   const int64_t r = walk_next(s, w);
   w.today_ok = false;
+  CW_DAY_PLAIN(w.day_plain = false;)
   w.dm_ok = false;
   return r;
 }

@@ -169,6 +169,7 @@ CW_HD void chain_fast_forward(const Spec& s, Walk& w, int64_t limit, uint32_t* m
   w.t = (int64_t)last_dn * 86400 + last_sod - w.off;
   civil_from_days(last_dn, w.Y, w.M, w.D);
   w.today_ok = true;  // last_dn came out of the month's day mask
+  CW_DAY_PLAIN(w.day_plain = false;)
   w.dm_ok = false;
 }
 

@@ -17,11 +17,14 @@ _TABLES = {}
 def lib():
     global _LIB
     if _LIB is None:
-        so = os.path.join(HERE, "host_shim", "libwalk_host.so")
+        # B200CRON_SHIM_FLAGS: extra -D flags for the walk (e.g. -DB200CRON_WALK_DAY_PLAIN=1), built into its own .so
+        extra = os.environ.get("B200CRON_SHIM_FLAGS", "").split()
+        tag = "".join(c if c.isalnum() else "_" for c in "".join(extra))
+        so = os.path.join(HERE, "host_shim", f"libwalk_host{tag}.so")
         srcs = [os.path.join(HERE, "host_shim", "walk_host.cpp"), os.path.join(CSRC, "zone_table.cpp")]
         deps = srcs + [os.path.join(CSRC, f) for f in ("cron_walk.cuh", "unmet_walk.cuh", "zone_table.h")]
         if not os.path.exists(so) or any(os.path.getmtime(d) > os.path.getmtime(so) for d in deps):
-            subprocess.check_call(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-I" + CSRC, "-o", so] + srcs)
+            subprocess.check_call(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-I" + CSRC] + extra + ["-o", so] + srcs)
         L = C.CDLL(so)
         L.shim_table_build.restype = C.c_void_p
         L.shim_table_build.argtypes = [C.c_char_p, C.c_int]
