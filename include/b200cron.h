@@ -157,7 +157,11 @@ int b200cron_ctx_set_overlap(b200cron_ctx* ctx, int on);
  *   deadline may be NULL (Allow, 0, 0, nil).
  * Outputs per Cron: last (lastMissed, ZERO when none), next (Next(now)), missed (missedTimes, saturating at
  * UINT32_MAX; the caller emits TooManyMissedTimes when > 100, :431-434), status, decision.  RequeueAfter is
- * next - now (:192).  Gated Crons get ZERO times and missed 0. */
+ * next - now (:192).  Gated Crons get ZERO times and missed 0.
+ * Two kernels run per call: one answers the Crons whose chain the closed form can follow, the other runs the general
+ * walk over the rest, which reach it through an index list in device memory owned by the context (4 bytes per Cron
+ * of the largest batch seen, three lists per device, allocated when a larger batch first arrives; calls on different
+ * streams are kept apart by events). */
 int b200cron_unmet_since(b200cron_ctx* ctx, const uint64_t* const masks[6], const int32_t* zone_id,
                          const int64_t* earliest, int64_t now, int32_t now_nsec, const uint8_t* policy,
                          const uint32_t* active, const uint8_t* flags, const int64_t* deadline, size_t n,
