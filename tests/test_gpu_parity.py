@@ -57,6 +57,23 @@ def test_golden_vectors(ctx, names):
         assert perm.tolist() == c["perm"] and keep.tolist() == c["keep"]
 
 
+def test_upstream_robfig_vectors(ctx, names):
+    """robfig/cron v3.0.1's own TestNext / TestActivation rows ([UPSTREAM-RECALLED], tests/golden/upstream_robfig.json)
+    through b200cron_parse_* and b200cron_next_n on the GPU: expected values from outside this repository"""
+    U = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "upstream_robfig.json")))
+    specs = [api._parse(c["spec"], True) for c in U["next"]]
+    zid = np.array([names.index(s.Location or c["zone"]) for s, c in zip(specs, U["next"])], np.int32)
+    frm = np.array([c["from"] for c in U["next"]], np.int64)
+    want = np.array([po.ZERO if c["want"] is None else c["want"] for c in U["next"]], np.int64)
+    got = ctx.next_n(api.pack_specs(specs), frm, 1, zid)[:, 0]
+    bad = np.nonzero(got != want)[0]
+    assert len(bad) == 0, [(U["next"][b]["time"], U["next"][b]["spec"], int(got[b]), int(want[b])) for b in bad[:5]]
+    specs = [api._parse(c["spec"], False) for c in U["activation"]]
+    at = np.array([c["at"] for c in U["activation"]], np.int64)
+    got = ctx.next_n(api.pack_specs(specs), at - 1, 1)[:, 0]
+    assert ((got == at) == np.array([c["expected"] for c in U["activation"]])).all()
+
+
 def test_reference_shapes(ctx):
     """the reference's own known-answer tests, written against the mirrored interface"""
     now = ts(2026, 1, 1, 12)
