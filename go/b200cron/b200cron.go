@@ -19,7 +19,9 @@ import (
 	"errors"
 	"fmt"
 	"math"
+	"os"
 	"runtime"
+	"strings"
 	"time"
 	"unsafe"
 )
@@ -60,13 +62,51 @@ func NewEngine(devices []int, zoneinfoDir string) (*Engine, error) {
 		return nil, fmt.Errorf("b200cron: %s", C.GoString(C.b200cron_last_error(nil)))
 	}
 	e := &Engine{ctx: ctx}
-	if name := time.Local.String(); name != "Local" {
-		if id := e.ZoneID(name); id >= 0 {
-			e.local = id
-		}
+	// time.Local.String() is "Local" whenever Go loaded the zone from /etc/localtime (which is how the chart's
+	// useHostTimezone mounts it), so the IANA name has to be found the way Go's own zoneinfo_unix.go finds the data:
+	// $TZ first, then /etc/localtime.  A host zone that is not UTC and cannot be named is an error, never UTC.
+	name := localZoneName()
+	if id := e.ZoneID(name); name != "" && id >= 0 {
+		e.local = id
+	} else if _, off := time.Now().Zone(); off != 0 || !isUTCAllYear() {
+		e.Close()
+		return nil, fmt.Errorf("b200cron: cannot map time.Local to an IANA zone (TZ=%q, /etc/localtime -> %q)",
+			os.Getenv("TZ"), name)
 	}
 	runtime.SetFinalizer(e, func(e *Engine) { e.Close() })
 	return e, nil
+}
+
+// localZoneName returns the IANA name behind time.Local: $TZ (":Name" or "Name"), else the target of the
+// /etc/localtime symlink below a zoneinfo directory; "" when neither names a zone (a copied file, for instance).
+func localZoneName() string {
+	if tz, ok := os.LookupEnv("TZ"); ok {
+		tz = strings.TrimPrefix(tz, ":")
+		if tz == "" {
+			return "UTC" // Go: TZ="" means UTC
+		}
+		if i := strings.Index(tz, "zoneinfo/"); strings.HasPrefix(tz, "/") && i >= 0 {
+			return tz[i+len("zoneinfo/"):]
+		}
+		return tz
+	}
+	if target, err := os.Readlink("/etc/localtime"); err == nil {
+		if i := strings.Index(target, "zoneinfo/"); i >= 0 {
+			return target[i+len("zoneinfo/"):]
+		}
+	}
+	return ""
+}
+
+// isUTCAllYear reports whether time.Local has offset 0 at both solstices (an unnamed zone that is UTC in effect).
+func isUTCAllYear() bool {
+	y := time.Now().Year()
+	for _, m := range []time.Month{time.January, time.July} {
+		if _, off := time.Date(y, m, 1, 0, 0, 0, 0, time.Local).Zone(); off != 0 {
+			return false
+		}
+	}
+	return true
 }
 
 func (e *Engine) Close() {

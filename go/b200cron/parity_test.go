@@ -10,6 +10,7 @@ package b200cron
 import (
 	"encoding/json"
 	"os"
+	"strings"
 	"testing"
 	"time"
 
@@ -64,6 +65,25 @@ func TestDump(t *testing.T) {
 					t.Errorf("%q %s from %d [%d]: robfig %d, oracle %d", c.Spec, c.Zone, f, j, got, c.Want[i][j])
 				}
 			}
+		}
+	}
+}
+
+// TestLocalZoneName: time.Local.String() is "Local" under a mounted /etc/localtime, so the shim must find the name
+// itself; with TZ unset the answer comes from the /etc/localtime symlink (run on a host whose localtime is not UTC).
+func TestLocalZoneName(t *testing.T) {
+	t.Setenv("TZ", ":Europe/Berlin")
+	if got := localZoneName(); got != "Europe/Berlin" {
+		t.Fatalf("TZ=:Europe/Berlin -> %q", got)
+	}
+	t.Setenv("TZ", "")
+	if got := localZoneName(); got != "UTC" {
+		t.Fatalf("TZ= -> %q", got)
+	}
+	os.Unsetenv("TZ")
+	if target, err := os.Readlink("/etc/localtime"); err == nil && strings.Contains(target, "zoneinfo/") {
+		if got := localZoneName(); !strings.HasSuffix(target, got) || got == "" {
+			t.Fatalf("/etc/localtime -> %q, got %q", target, got)
 		}
 	}
 }
