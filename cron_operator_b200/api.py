@@ -28,6 +28,7 @@ ST_OK, ST_UNSCHEDULABLE, ST_EARLIEST_AFTER_NOW, ST_NONTERMINATING = 0, 1, 2, 3
 POLICY = {"Allow": 0, "Forbid": 1, "Replace": 2, "": 0}  # api/v1alpha1/cron_types.go:127-139
 FLAG_SUSPEND, FLAG_DELETED = 1, 2
 KIND_SPEC, KIND_EVERY = 0, 1
+EVERY_TAG = 1 << 62  # B200CRON_EVERY_TAG: month plane of a ConstantDelaySchedule, its delay (seconds) in the dom plane
 
 
 class B200CronError(RuntimeError):
@@ -51,13 +52,13 @@ def lib_path() -> str:
     return _build.LIB
 
 
-def lib():
-    """Loads csrc/libb200cron.so (building it with nvcc when sources are newer).  Fails loudly when unavailable."""
+def lib(path: str | None = None):
+    """Loads csrc/libb200cron.so (building it with nvcc when sources are newer).  Fails loudly when unavailable.
+    `path`: load that build instead (first call only; the A/B scripts under profiles/ pass their tuning builds)."""
     global _LIB
     if _LIB is not None:
         return _LIB
-    path = os.environ.get("B200CRON_LIB") or _build.build()  # B200CRON_LIB: tuning builds (see profiles/)
-    L = C.CDLL(path)
+    L = C.CDLL(path or _build.build())
     vp, sz, i32, i64 = C.c_void_p, C.c_size_t, C.c_int, C.c_int64
     for f in (L.b200cron_parse_standard, L.b200cron_parse_with_seconds):
         f.restype = i32
@@ -106,6 +107,19 @@ def lib():
     L.b200cron_parse_batch.argtypes = [vp, vp, vp, sz, i32, vp, vp, vp, vp]
     L.b200cron_parse_batch_dev.restype = i32
     L.b200cron_parse_batch_dev.argtypes = [vp, i32, vp, vp, vp, sz, i32, vp, vp, vp, vp]
+    L.b200cron_specset_create.restype = i32
+    L.b200cron_specset_create.argtypes = [vp, vp, vp, sz, C.POINTER(vp)]
+    L.b200cron_specset_update.restype = i32
+    L.b200cron_specset_update.argtypes = [vp, sz, sz, vp, vp]
+    L.b200cron_specset_destroy.argtypes = [vp]
+    L.b200cron_specset_size.restype = sz
+    L.b200cron_specset_size.argtypes = [vp]
+    L.b200cron_next_n_set.restype = i32
+    L.b200cron_next_n_set.argtypes = [vp, vp, vp, i32, vp]
+    L.b200cron_unmet_since_set.restype = i32
+    L.b200cron_unmet_since_set.argtypes = [vp, vp, vp, i64, C.c_int32, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+    L.b200cron_debug_last_deferred.restype = i32
+    L.b200cron_debug_last_deferred.argtypes = [vp, i32, vp, vp, sz, C.POINTER(sz)]
     L.b200cron_sync_check.restype = i32
     L.b200cron_sync_check.argtypes = [vp, i32, vp]
     L.b200cron_ctx_set_overlap.restype = i32
@@ -132,6 +146,9 @@ class SpecSchedule:
     Every: int = 0  # > 0: ConstantDelaySchedule{Delay: Every seconds} from "@every <dur>"
 
     def masks(self):
+        """the six planes as the batched calls take them (a ConstantDelaySchedule in its B200CRON_EVERY_TAG encoding)"""
+        if self.Every:
+            return (0, 0, 0, self.Every, EVERY_TAG, 0)
         return (self.Second, self.Minute, self.Hour, self.Dom, self.Month, self.Dow)
 
 
@@ -143,8 +160,10 @@ def _parse(text, with_seconds) -> SpecSchedule:
     rc = fn(b, len(b), C.byref(spec), C.byref(kind), C.byref(every), tz, 128, err, 512)
     if rc != 0:
         raise ParseError(err.value.decode(errors="replace"))
-    return SpecSchedule(spec.second, spec.minute, spec.hour, spec.dom, spec.month, spec.dow, tz.value.decode(),
-                        every.value if kind.value == KIND_EVERY else 0)
+    if kind.value == KIND_EVERY:
+        assert (spec.month, spec.dom) == (EVERY_TAG, every.value)
+        return SpecSchedule(0, 0, 0, 0, 0, 0, tz.value.decode(), every.value)
+    return SpecSchedule(spec.second, spec.minute, spec.hour, spec.dom, spec.month, spec.dow, tz.value.decode(), 0)
 
 
 def ParseStandard(spec: str) -> SpecSchedule:
@@ -328,6 +347,10 @@ class Context:
                                                  len(seg_off) - 1, perm.ctypes.data, keep.ctypes.data))
         return perm, keep
 
+    # ---- resident spec sets: the immutable masks stay in HBM, a tick moves only times in and results out
+    def specset(self, masks: np.ndarray, zone_id=None, five_field: bool = False) -> "SpecSet":
+        return SpecSet(self, masks, zone_id, five_field)
+
     # ---- device-pointer calls (torch tensors resident on device `dev_index`; enqueue only)
     def next_n_dev(self, masks, from_, out, k: int = 1, zone_id=None, dev_index: int = 0, stream: int = 0,
                    five_field: bool = False):
@@ -352,7 +375,8 @@ class Context:
     # ---- batched ParseStandard on the device
     def parse_batch(self, specs, with_seconds: bool = False):
         """cronv3.ParseStandard over a list of schedule strings on the GPU.  Returns (masks (6, n) uint64, status (n,)
-        uint8: 0 ok / 1 unparsable / 2 @every, tz names list (None when the spec has no TZ= prefix))."""
+        uint8: 0 ok (an "@every" with plain h/m/s terms comes back in the EVERY_TAG encoding) / 1 unparsable / 2 an
+        "@every" duration only the host parser handles, tz names list (None when the spec has no TZ= prefix))."""
         enc = [s.encode() if isinstance(s, str) else bytes(s) for s in specs]
         n = len(enc)
         off = np.zeros(n + 1, dtype=np.uint64)
@@ -386,7 +410,10 @@ class Context:
                 continue
             if tz[i] not in (None, "Local"):
                 self.zone_id(tz[i])  # time.LoadLocation error for unknown names
-            out.append(SpecSchedule(*[int(masks[p, i]) for p in range(6)], tz[i] or "", 0))
+            if int(masks[4, i]) == EVERY_TAG:  # "@every 1h30m" parsed on the device
+                out.append(SpecSchedule(0, 0, 0, 0, 0, 0, tz[i] or "", int(masks[3, i])))
+            else:
+                out.append(SpecSchedule(*[int(masks[p, i]) for p in range(6)], tz[i] or "", 0))
         return out
 
     # ---- device-side synthetic workloads (bit-identical to synth.py)
@@ -413,14 +440,19 @@ class Context:
         promises they are independent batches -- see include/b200cron.h)"""
         self._check(lib().b200cron_ctx_set_overlap(self._h, 1 if on else 0))
 
+    def last_deferred(self, cap: int = 1 << 24, dev_index: int = 0, stream: int = 0):
+        """test support: (indices, count) of the Crons the most recent unmet launch handed to the general walk"""
+        cnt = C.c_size_t()
+        buf = np.empty(cap, np.uint32)
+        self._check(lib().b200cron_debug_last_deferred(self._h, dev_index, stream or None, buf.ctypes.data, cap, C.byref(cnt)))
+        return buf[:min(cap, cnt.value)].copy(), int(cnt.value)
+
     def sync_check(self, dev_index: int = 0, stream: int = 0):
         self._check(lib().b200cron_sync_check(self._h, dev_index, stream or None))
 
     # ---- the reference's scalar shapes, served by the batched kernels (n = 1: launch latency >> one CPU Next)
     def Next(self, sched: SpecSchedule, t: int) -> int:
-        """Schedule.Next(t) (cron_controller.go:405,436)"""
-        if sched.Every:
-            return t + sched.Every  # constantdelay.go: t.Add(Delay - t.Nanosecond())
+        """Schedule.Next(t) (cron_controller.go:405,436), either kind of schedule"""
         return int(self.NextN([sched], [t], 1)[0, 0])
 
     def NextN(self, specs, from_, k: int) -> np.ndarray:
@@ -457,6 +489,54 @@ class Context:
         lim = np.array([-1 if history_limit is None else history_limit], dtype=np.int64)
         perm, keep = self.history_prune(np.array([0, len(ts)], dtype=np.uint64), ts, lim)
         return perm[keep == 0], perm[keep == 1]
+
+
+class SpecSet:
+    """b200cron_specset: n schedules resident on the context's devices (SpecSchedule is immutable after ParseStandard,
+    cron_controller.go:392); next_n / unmet_since over them move only the per-tick arrays"""
+
+    def __init__(self, ctx: Context, masks: np.ndarray, zone_id=None, five_field: bool = False):
+        self.ctx, self._h = ctx, C.c_void_p()
+        planes, n = _planes(masks, five_field)
+        zid = None if zone_id is None else np.ascontiguousarray(zone_id, dtype=np.int32)
+        ctx._check(lib().b200cron_specset_create(ctx._h, planes, _ptr(zid), n, C.byref(self._h)))
+        self.n, self.five_field, self.zoned = n, five_field, zone_id is not None
+
+    def close(self):
+        if self._h:
+            lib().b200cron_specset_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __len__(self):
+        return int(lib().b200cron_specset_size(self._h))
+
+    def update(self, first: int, masks: np.ndarray, zone_id=None):
+        planes, count = _planes(masks, self.five_field)
+        zid = None if zone_id is None else np.ascontiguousarray(zone_id, dtype=np.int32)
+        self.ctx._check(lib().b200cron_specset_update(self._h, first, count, planes, _ptr(zid)))
+
+    def next_n(self, from_, k: int = 1, out=None) -> np.ndarray:
+        from_ = np.ascontiguousarray(from_, dtype=np.int64)
+        if out is None:
+            out = np.empty((self.n, k), dtype=np.int64)
+        self.ctx._check(lib().b200cron_next_n_set(self.ctx._h, self._h, from_.ctypes.data, k, out.ctypes.data))
+        return out
+
+    def unmet_since(self, earliest, now: int, now_nsec: int = 0, policy=None, active=None, flags=None, deadline=None,
+                    out=None) -> dict:
+        cv = lambda a, dt: None if a is None else np.ascontiguousarray(a, dtype=dt)  # noqa: E731
+        earliest = cv(earliest, np.int64)
+        policy, active, flags, deadline = cv(policy, np.uint8), cv(active, np.uint32), cv(flags, np.uint8), cv(deadline, np.int64)
+        n = self.n
+        if out is None:
+            out = dict(last=np.empty(n, np.int64), next=np.empty(n, np.int64), missed=np.empty(n, np.uint32),
+                       status=np.empty(n, np.uint8), decision=np.empty(n, np.uint8))
+        self.ctx._check(lib().b200cron_unmet_since_set(self.ctx._h, self._h, earliest.ctypes.data, now, now_nsec,
+                                                       _ptr(policy), _ptr(active), _ptr(flags), _ptr(deadline),
+                                                       out["last"].ctypes.data, out["next"].ctypes.data,
+                                                       out["missed"].ctypes.data, out["status"].ctypes.data,
+                                                       out["decision"].ctypes.data))
+        return out
 
 
 def getDefaultJobName(cron_name: str, schedule_time: int) -> str:

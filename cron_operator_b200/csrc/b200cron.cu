@@ -13,6 +13,7 @@
 #include <cstring>
 #include <mutex>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "../../include/b200cron.h"
@@ -28,7 +29,10 @@ using namespace b200cron;
 constexpr int kSlots = 3;
 constexpr size_t kChunk = 1u << 18;  // specs per pipelined chunk of the host-pointer calls
 
-std::string g_create_error;
+// Error text of the calling thread's last failed call: entry points validate their arguments before they take the
+// context's mutex, and callers on different threads (cgo runs Reconcile on up to MaxConcurrentReconciles OS threads)
+// must not see each other's messages.
+thread_local std::string t_error;
 
 struct Slot {
   cudaStream_t stream = nullptr;
@@ -44,20 +48,18 @@ struct DeferList {
   uint32_t* count = nullptr;
   size_t cap = 0;  // entries
   cudaEvent_t done = nullptr;
-  // opt-in zone order (B200CRON_UNMET_ZONE_ORDER=1): Cron indices grouped by zone id, and 2 x nzones counters
-  uint32_t* order = nullptr;
-  size_t order_cap = 0;
-  uint32_t* zone_counts = nullptr;
 };
 constexpr int kDeferLists = 3;
 
 struct Device {
   int id = 0;
+  int sm_count = 148;
   cudaStream_t stream = nullptr;  // default stream of the _dev entry points
   int64_t* d_when = nullptr;
   int32_t* d_off = nullptr;
   int32_t* d_fpre = nullptr;
   int32_t* d_zstart = nullptr;
+  uint16_t* d_yidx = nullptr;
   int* d_err = nullptr;
   int* h_err = nullptr;  // pinned mirror
   Slot slots[kSlots];
@@ -65,6 +67,7 @@ struct Device {
   size_t scratch_cap = 0;         // entries
   DeferList defer[kDeferLists];       // scratch of the unmet kernel pair, handed out round-robin (see launch_unmet)
   int defer_next = 0;
+  int defer_last = -1;  // the list the most recent unmet launch used (b200cron_debug_last_deferred)
   uint64_t* d_static_sums = nullptr;  // device address of g_static_tile_sums on this device (resolved on first use)
   ZoneTable zt{};
 };
@@ -74,7 +77,6 @@ struct Device {
 struct b200cron_ctx {
   std::vector<Device> devs;
   HostZoneTable zones;
-  std::string error;
   std::mutex mu;
   std::atomic<uint64_t> launches{0};
   std::atomic<int> overlap{0};  // b200cron_ctx_set_overlap
@@ -88,7 +90,8 @@ int fail(b200cron_ctx* ctx, int code, const char* fmt, ...) {
   va_start(ap, fmt);
   vsnprintf(buf, sizeof buf, fmt, ap);
   va_end(ap);
-  if (ctx) ctx->error = buf; else g_create_error = buf;
+  (void)ctx;
+  t_error = buf;
   return code;
 }
 
@@ -111,13 +114,36 @@ int ensure_slot(b200cron_ctx* ctx, Slot& s, size_t bytes) {
   return 0;
 }
 
-bool is_pinned_host(const void* p) {
+// Pinned (page-locked, mapped) host memory?  *dev receives the address kernels on the CURRENT device must use for
+// it: equal to the host address under unified addressing, but not for cudaHostRegister'd memory on systems where
+// canUseHostPointerForRegisteredMem is 0.
+bool pinned_alias(const void* p, const void** dev) {
   cudaPointerAttributes a;
   if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
-  return a.type == cudaMemoryTypeHost;
+  if (a.type != cudaMemoryTypeHost || a.devicePointer == nullptr) return false;
+  *dev = a.devicePointer;
+  return true;
 }
+bool is_pinned_host(const void* p) {
+  const void* d;
+  return pinned_alias(p, &d);
+}
+template <typename T>
+const T* dev_alias(const T* p) {  // p is known to be pinned (is_pinned_host) or NULL
+  const void* d = p;
+  if (p) pinned_alias(p, &d);
+  return static_cast<const T*>(d);
+}
+template <typename T>
+T* dev_alias(T* p) { return const_cast<T*>(dev_alias(static_cast<const T*>(p))); }
 
 bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// B200CRON_NEXTN_SPLIT (tuning builds): 1 = k > 1 launches walk class-pure warps (next_n_tile_kernel, one launch per
+// class); 0 = one launch of next_n_kernel over the specs in input order.
+#ifndef B200CRON_NEXTN_SPLIT
+#define B200CRON_NEXTN_SPLIT 1
+#endif
 
 // ---- launches -------------------------------------------------------------------------------------------------
 template <int KT>
@@ -136,15 +162,23 @@ cudaError_t launch_next_kt(bool vec, unsigned grid, size_t smem, cudaStream_t st
   return cudaGetLastError();
 }
 
+// B200CRON_NEXT1_RING (tuning builds): 1 = k == 1 launches on device-resident inputs use the persistent kernel with the
+// asynchronous input ring (next1_ring_kernel); 0 = always next1_kernel.
+#ifndef B200CRON_NEXT1_RING
+#define B200CRON_NEXT1_RING 1
+#endif
+
+// device_resident: every buffer lives in this device's memory (the bulk-copy ring reads this GPU's memory only;
+// pinned host buffers used in place take the plain-load kernel)
 cudaError_t launch_next(b200cron_ctx* ctx, const Device& d, cudaStream_t st, const MaskPlanes& m, const int32_t* zone,
-                        const int64_t* from, size_t n, int k, int64_t* out) {
+                        const int64_t* from, size_t n, int k, int64_t* out, bool device_resident) {
   if (n == 0) return cudaSuccess;
   bool vec = aligned16(from) && aligned16(out) && (!zone || (reinterpret_cast<uintptr_t>(zone) & 7u) == 0);
   for (int p = 0; p < 6; ++p) vec = vec && (m.p[p] == nullptr || aligned16(m.p[p]));
   const unsigned grid = (unsigned)((n + kNextTile - 1) / kNextTile);
   const size_t smem = (k == 1 || !kNextStage) ? 0 : (size_t)kNextTile * k * sizeof(int64_t);
   ctx->launches.fetch_add(1, std::memory_order_relaxed);
-  if (k == 1 && !getenv("B200CRON_NEXT1_PAIRED")) {  // one spec per lane (finer waves); the env var selects the paired kernel
+  if (k == 1) {  // one spec per lane (finer waves than next_n_kernel's two)
     const unsigned g1 = (unsigned)((n + kNext1Threads - 1) / kNext1Threads);
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(g1);
@@ -155,11 +189,35 @@ cudaError_t launch_next(b200cron_ctx* ctx, const Device& d, cudaStream_t st, con
     attr.val.programmaticStreamSerializationAllowed = 1;
     if (ctx->overlap.load(std::memory_order_relaxed)) { cfg.attrs = &attr; cfg.numAttrs = 1; }
     int* err = d.d_err;
+    if (B200CRON_NEXT1_RING && device_resident && vec && (!zone || aligned16(zone)) && n >= 32) {
+      const size_t cta_tiles = (n / 32 + kRingWarps - 1) / kRingWarps;
+      const size_t resident = (size_t)d.sm_count * B200CRON_RING_MINBLOCKS;
+      cfg.gridDim = dim3((unsigned)(cta_tiles < resident ? cta_tiles : resident));
+      cfg.blockDim = dim3(kRingThreads);
+      cfg.dynamicSmemBytes = kRingSmemBytes;
+      if (zone) return cudaLaunchKernelEx(&cfg, next1_ring_kernel<false>, m, zone, from, n, out, d.zt, err);
+      return cudaLaunchKernelEx(&cfg, next1_ring_kernel<true>, m, zone, from, n, out, d.zt, err);
+    }
     if (zone) return cudaLaunchKernelEx(&cfg, next1_kernel<false>, m, zone, from, n, out, d.zt, err);
     return cudaLaunchKernelEx(&cfg, next1_kernel<true>, m, zone, from, n, out, d.zt, err);  // all-UTC launch
   }
+#if B200CRON_NEXTN_SPLIT
+  {  // k > 1: class-pure warps, one launch per class (kernels.cuh); a launch without zone ids is all UTC
+    const unsigned tgrid = (unsigned)((n + kNextTileSpecs - 1) / kNextTileSpecs);
+    auto go = [&](auto kt) {
+      constexpr int KT = decltype(kt)::value;
+      next_n_tile_kernel<KT, true><<<tgrid, kNextTileThreads, 0, st>>>(m, zone, from, n, k, out, d.zt, d.d_err);
+      if (zone) {
+        ctx->launches.fetch_add(1, std::memory_order_relaxed);
+        next_n_tile_kernel<KT, false><<<tgrid, kNextTileThreads, 0, st>>>(m, zone, from, n, k, out, d.zt, d.d_err);
+      }
+      return cudaGetLastError();
+    };
+    if (k == 16) return go(std::integral_constant<int, 16>{});
+    return go(std::integral_constant<int, 0>{});
+  }
+#endif
   switch (k) {
-    case 1: return launch_next_kt<1>(vec, grid, smem, st, m, zone, from, n, k, out, d.zt, d.d_err);
     case 2: return launch_next_kt<2>(vec, grid, smem, st, m, zone, from, n, k, out, d.zt, d.d_err);
     case 4: return launch_next_kt<4>(vec, grid, smem, st, m, zone, from, n, k, out, d.zt, d.d_err);
     case 8: return launch_next_kt<8>(vec, grid, smem, st, m, zone, from, n, k, out, d.zt, d.d_err);
@@ -169,66 +227,72 @@ cudaError_t launch_next(b200cron_ctx* ctx, const Device& d, cudaStream_t st, con
   }
 }
 
+// B200CRON_UNMET_PLAN (tuning builds, profiles/build_variants.sh): 0 = the tile kernel handles both classes in input
+// order; 1 = the tile kernel handles the UTC class, the zoned class goes through a zone-ordered index list.
+#ifndef B200CRON_UNMET_PLAN
+#define B200CRON_UNMET_PLAN 1
+#endif
+
 cudaError_t launch_unmet(b200cron_ctx* ctx, Device& d, cudaStream_t st, const UnmetArgs& a) {
   if (a.n == 0) return cudaSuccess;
-  const unsigned grid = (unsigned)((a.n + kUnmetThreads - 1) / kUnmetThreads);
-  static const bool single = getenv("B200CRON_UNMET_SINGLE") != nullptr;  // one general kernel, no scratch (tuning)
-  if (single || a.n > 0xffffffffULL) {
+  if (a.n > 0xffffffffULL) {  // beyond the 32-bit index lists: one launch of the general machine, no scratch
     ctx->launches.fetch_add(1, std::memory_order_relaxed);
-    unmet_kernel<kUnmetSingle><<<grid, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, nullptr, nullptr);
+    unmet_single_kernel<<<(unsigned)((a.n + kUnmetThreads - 1) / kUnmetThreads), kUnmetThreads, 0, st>>>(a, d.zt, d.d_err);
+    return cudaGetLastError();
+  }
+  const unsigned tiles = (unsigned)((a.n + kUnmetTile - 1) / kUnmetTile);
+  if (!a.zone_id) {  // every Cron in UTC: the closed form always answers, nothing can be deferred, no scratch
+    ctx->launches.fetch_add(1, std::memory_order_relaxed);
+    unmet_tile_kernel<false><<<tiles, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, nullptr, nullptr);
     return cudaGetLastError();
   }
   DeferList& b = d.defer[d.defer_next];
+  d.defer_last = d.defer_next;
   d.defer_next = (d.defer_next + 1) % kDeferLists;
   cudaError_t e;
+  const int32_t nz = d.zt.nzones;
   if (!b.done) {
     if ((e = cudaEventCreateWithFlags(&b.done, cudaEventDisableTiming)) != cudaSuccess) return e;
-    if ((e = cudaMalloc(&b.count, sizeof(uint32_t))) != cudaSuccess) return e;
+    // counters: [0] defer count | [1 .. nz] zone histogram | [nz+1 .. 2nz+1] cursors, the last one = ordered-list length
+    if ((e = cudaMalloc(&b.count, (2 * (size_t)nz + 2) * sizeof(uint32_t))) != cudaSuccess) return e;
   } else if ((e = cudaStreamWaitEvent(st, b.done, 0)) != cudaSuccess) {
     return e;
   }
-  if (a.n > b.cap) {  // every Cron of the launch may be deferred
+  const bool ordered = B200CRON_UNMET_PLAN == 1;
+  const size_t need = ordered ? 2 * a.n : a.n;  // defer list (every Cron may be deferred) [+ zone-ordered list]
+  if (need > b.cap) {
     if (b.idx) {
       if ((e = cudaEventSynchronize(b.done)) != cudaSuccess) return e;
       if ((e = cudaFree(b.idx)) != cudaSuccess) return e;
       b.idx = nullptr;
       b.cap = 0;
     }
-    if ((e = cudaMalloc(&b.idx, a.n * sizeof(uint32_t))) != cudaSuccess) return e;
-    b.cap = a.n;
+    if ((e = cudaMalloc(&b.idx, need * sizeof(uint32_t))) != cudaSuccess) return e;
+    b.cap = need;
   }
-  if ((e = cudaMemsetAsync(b.count, 0, sizeof(uint32_t), st)) != cudaSuccess) return e;
-  static const bool zone_order = getenv("B200CRON_UNMET_ZONE_ORDER") != nullptr;  // opt-in, see kernels.cuh
-  if (zone_order && a.zone_id) {
-    const int32_t nz = d.zt.nzones;
-    if (!b.zone_counts && (e = cudaMalloc(&b.zone_counts, 2 * (size_t)nz * sizeof(uint32_t))) != cudaSuccess) return e;
-    if (a.n > b.order_cap) {
-      if (b.order) {
-        if ((e = cudaEventSynchronize(b.done)) != cudaSuccess) return e;
-        if ((e = cudaFree(b.order)) != cudaSuccess) return e;
-        b.order = nullptr;
-        b.order_cap = 0;
-      }
-      if ((e = cudaMalloc(&b.order, a.n * sizeof(uint32_t))) != cudaSuccess) return e;
-      b.order_cap = a.n;
-    }
-    uint32_t* hist = b.zone_counts;
-    uint32_t* cursor = b.zone_counts + nz;
-    if ((e = cudaMemsetAsync(hist, 0, (size_t)nz * sizeof(uint32_t), st)) != cudaSuccess) return e;
+  const unsigned grid = (unsigned)((a.n + kUnmetThreads - 1) / kUnmetThreads);
+  if (ordered) {
+    uint32_t* hist = b.count + 1;
+    uint32_t* cursor = hist + nz;
+    uint32_t* order = b.idx + a.n;
+    if ((e = cudaMemsetAsync(b.count, 0, (size_t)(nz + 1) * sizeof(uint32_t), st)) != cudaSuccess) return e;
     const unsigned zgrid = (unsigned)((a.n + kZoneOrderTile - 1) / kZoneOrderTile);
-    ctx->launches.fetch_add(5, std::memory_order_relaxed);
+    ctx->launches.fetch_add(6, std::memory_order_relaxed);
     zone_order_hist_kernel<<<zgrid, kZoneOrderThreads, (size_t)nz * sizeof(uint32_t), st>>>(a.zone_id, a.n, nz, hist);
     zone_order_scan_kernel<<<1, kZoneOrderThreads, 0, st>>>(hist, nz, cursor);
     zone_order_scatter_kernel<<<zgrid, kZoneOrderThreads, 2 * (size_t)nz * sizeof(uint32_t), st>>>(a.zone_id, a.n, nz,
-                                                                                                  cursor, b.order);
-    unmet_kernel<kUnmetEasy, true><<<grid, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, b.idx, b.count, b.order);
+                                                                                                  cursor, order);
+    unmet_tile_kernel<false><<<tiles, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, nullptr, nullptr);
+    // the scatter advanced cursor[z] to the end of zone z's range; cursor[nz] (the total) is untouched
+    unmet_ordered_kernel<<<grid, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, b.idx, b.count, order, cursor + nz);
   } else {
+    if ((e = cudaMemsetAsync(b.count, 0, sizeof(uint32_t), st)) != cudaSuccess) return e;
     ctx->launches.fetch_add(2, std::memory_order_relaxed);
-    unmet_kernel<kUnmetEasy><<<grid, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, b.idx, b.count);
+    unmet_tile_kernel<true><<<tiles, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, b.idx, b.count);
   }
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
-  const unsigned hard_grid = grid < 148u * 12u ? grid : 148u * 12u;
-  unmet_hard_kernel<<<hard_grid, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, b.idx, b.count);
+  const unsigned hard_max = (unsigned)d.sm_count * B200CRON_UNMET_HARD_MINBLOCKS;
+  unmet_hard_kernel<<<grid < hard_max ? grid : hard_max, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, b.idx, b.count);
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
   return cudaEventRecord(b.done, st);
 }
@@ -329,12 +393,15 @@ extern "C" int b200cron_ctx_create(const int* devices, int ndev, const char* zon
     }                                                                                                   \
   } while (0)
     CUC(cudaSetDevice(d.id));
+    CUC(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, d.id));
     CUC(cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking));
     for (Slot& s : d.slots) CUC(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
     CUC(cudaMalloc(&d.d_when, z.when.size() * sizeof(int64_t)));
     CUC(cudaMalloc(&d.d_off, z.off.size() * sizeof(int32_t)));
     CUC(cudaMalloc(&d.d_fpre, z.fpre.size() * sizeof(int32_t)));
     CUC(cudaMalloc(&d.d_zstart, z.zstart.size() * sizeof(int32_t)));
+    CUC(cudaMalloc(&d.d_yidx, z.yidx.size() * sizeof(uint16_t)));
+    CUC(cudaMemcpy(d.d_yidx, z.yidx.data(), z.yidx.size() * sizeof(uint16_t), cudaMemcpyHostToDevice));
     CUC(cudaMalloc(&d.d_err, sizeof(int)));
     CUC(cudaHostAlloc(&d.h_err, sizeof(int), cudaHostAllocDefault));
     *d.h_err = 0;
@@ -348,6 +415,8 @@ extern "C" int b200cron_ctx_create(const int* devices, int ndev, const char* zon
     d.zt.off = d.d_off;
     d.zt.fpre = d.d_fpre;
     d.zt.zstart = d.d_zstart;
+    d.zt.yidx = d.d_yidx;
+    d.zt.ystride = z.ystride;
     d.zt.nzones = (int32_t)z.names.size();
     d.zt.horizon = z.horizon;
   }
@@ -368,13 +437,12 @@ extern "C" void b200cron_ctx_destroy(b200cron_ctx* ctx) {
     if (d.d_off) cudaFree(d.d_off);
     if (d.d_fpre) cudaFree(d.d_fpre);
     if (d.d_zstart) cudaFree(d.d_zstart);
+    if (d.d_yidx) cudaFree(d.d_yidx);
     if (d.d_err) cudaFree(d.d_err);
     if (d.d_scratch) cudaFree(d.d_scratch);
     for (DeferList& b : d.defer) {
       if (b.idx) cudaFree(b.idx);
       if (b.count) cudaFree(b.count);
-      if (b.order) cudaFree(b.order);
-      if (b.zone_counts) cudaFree(b.zone_counts);
       if (b.done) cudaEventDestroy(b.done);
     }
     if (d.h_err) cudaFreeHost(d.h_err);
@@ -383,7 +451,8 @@ extern "C" void b200cron_ctx_destroy(b200cron_ctx* ctx) {
 }
 
 extern "C" const char* b200cron_last_error(const b200cron_ctx* ctx) {
-  return ctx ? ctx->error.c_str() : g_create_error.c_str();
+  (void)ctx;
+  return t_error.c_str();
 }
 extern "C" int b200cron_device_count(const b200cron_ctx* ctx) { return ctx ? (int)ctx->devs.size() : 0; }
 extern "C" int b200cron_zone_id(const b200cron_ctx* ctx, const char* name) {
@@ -443,12 +512,14 @@ extern "C" int b200cron_next_n_dev(b200cron_ctx* ctx, int dev_index, void* strea
   Device* d = device_at(ctx, dev_index);
   if (!d) return B200CRON_EINVAL;
   if (!masks || !from || !out || k < 1 || k > 64) return fail(ctx, B200CRON_EINVAL, "next_n: bad argument (1 <= k <= 64)");
+  for (int p = 1; p < 6; ++p)
+    if (!masks[p]) return fail(ctx, B200CRON_EINVAL, "next_n: only the seconds plane (masks[0]) may be NULL");
   std::lock_guard<std::mutex> lk(ctx->mu);
   CU(ctx, cudaSetDevice(d->id));
   MaskPlanes m;
   for (int p = 0; p < 6; ++p) m.p[p] = masks[p];
   cudaStream_t st = stream ? (cudaStream_t)stream : d->stream;
-  CU(ctx, launch_next(ctx, *d, st, m, zone_id, from, n, k, out));
+  CU(ctx, launch_next(ctx, *d, st, m, zone_id, from, n, k, out, true));
   return B200CRON_OK;
 }
 
@@ -472,9 +543,9 @@ extern "C" int b200cron_next_n(b200cron_ctx* ctx, const uint64_t* const masks[6]
         if (sh.hi <= sh.lo) continue;
         CU(ctx, cudaSetDevice(d.id));
         MaskPlanes m;
-        for (int p = 0; p < 6; ++p) m.p[p] = masks[p] ? masks[p] + sh.lo : nullptr;
-        CU(ctx, launch_next(ctx, d, d.stream, m, zone_id ? zone_id + sh.lo : nullptr, from + sh.lo, sh.hi - sh.lo, k,
-                            out + sh.lo * (size_t)k));
+        for (int p = 0; p < 6; ++p) m.p[p] = masks[p] ? dev_alias(masks[p]) + sh.lo : nullptr;
+        CU(ctx, launch_next(ctx, d, d.stream, m, zone_id ? dev_alias(zone_id) + sh.lo : nullptr, dev_alias(from) + sh.lo,
+                            sh.hi - sh.lo, k, dev_alias(out) + sh.lo * (size_t)k, false));
         CU(ctx, collect_err(d, d.stream));
       }
       for (Device& d : ctx->devs) {
@@ -514,7 +585,7 @@ extern "C" int b200cron_next_n(b200cron_ctx* ctx, const uint64_t* const masks[6]
       }
       CU(ctx, cudaMemcpyAsync(d_from, from + c, cn * 8, cudaMemcpyHostToDevice, s.stream));
       if (zone_id) CU(ctx, cudaMemcpyAsync(d_zone, zone_id + c, cn * 4, cudaMemcpyHostToDevice, s.stream));
-      CU(ctx, launch_next(ctx, d, s.stream, m, zone_id ? d_zone : nullptr, d_from, cn, k, d_out));
+      CU(ctx, launch_next(ctx, d, s.stream, m, zone_id ? d_zone : nullptr, d_from, cn, k, d_out, true));
       CU(ctx, cudaMemcpyAsync(out + c * (size_t)k, d_out, cn * (size_t)k * 8, cudaMemcpyDeviceToHost, s.stream));
     }
   }
@@ -540,6 +611,8 @@ extern "C" int b200cron_unmet_since_dev(b200cron_ctx* ctx, int dev_index, void* 
   if (!d) return B200CRON_EINVAL;
   if (!masks || !earliest || !last || !next || !missed || !status || !decision)
     return fail(ctx, B200CRON_EINVAL, "unmet_since: NULL required argument");
+  for (int p = 1; p < 6; ++p)
+    if (!masks[p]) return fail(ctx, B200CRON_EINVAL, "unmet_since: only the seconds plane (masks[0]) may be NULL");
   std::lock_guard<std::mutex> lk(ctx->mu);
   CU(ctx, cudaSetDevice(d->id));
   UnmetArgs a{};
@@ -559,11 +632,13 @@ extern "C" int b200cron_unmet_since(b200cron_ctx* ctx, const uint64_t* const mas
   if (!ctx) return B200CRON_EINVAL;
   if (!masks || !earliest || !last || !next || !missed || !status || !decision)
     return fail(ctx, B200CRON_EINVAL, "unmet_since: NULL required argument");
+  for (int p = 1; p < 6; ++p)
+    if (!masks[p]) return fail(ctx, B200CRON_EINVAL, "unmet_since: only the seconds plane (masks[0]) may be NULL");
   std::lock_guard<std::mutex> lk(ctx->mu);
   const int G = (int)ctx->devs.size();
   {  // zero-copy when every buffer is pinned host memory (see b200cron_next_n)
-    const void* req[] = {masks[0], masks[1], masks[2], masks[3], masks[4], masks[5], earliest, last, next, missed, status, decision};
-    const void* opt[] = {zone_id, policy, active, flags, deadline};
+    const void* req[] = {masks[1], masks[2], masks[3], masks[4], masks[5], earliest, last, next, missed, status, decision};
+    const void* opt[] = {masks[0], zone_id, policy, active, flags, deadline};
     bool pinned = n > 0;
     for (const void* q : req) pinned = pinned && q && is_pinned_host(q);
     for (const void* q : opt) pinned = pinned && (!q || is_pinned_host(q));
@@ -574,14 +649,14 @@ extern "C" int b200cron_unmet_since(b200cron_ctx* ctx, const uint64_t* const mas
         if (sh.hi <= sh.lo) continue;
         CU(ctx, cudaSetDevice(d.id));
         UnmetArgs a{};
-        for (int p = 0; p < 6; ++p) a.m.p[p] = masks[p] + sh.lo;
-        a.zone_id = zone_id ? zone_id + sh.lo : nullptr;
-        a.earliest = earliest + sh.lo; a.now = now; a.now_nsec = now_nsec;
-        a.policy = policy ? policy + sh.lo : nullptr; a.active = active ? active + sh.lo : nullptr;
-        a.flags = flags ? flags + sh.lo : nullptr; a.deadline = deadline ? deadline + sh.lo : nullptr;
+        for (int p = 0; p < 6; ++p) a.m.p[p] = masks[p] ? dev_alias(masks[p]) + sh.lo : nullptr;
+        a.zone_id = zone_id ? dev_alias(zone_id) + sh.lo : nullptr;
+        a.earliest = dev_alias(earliest) + sh.lo; a.now = now; a.now_nsec = now_nsec;
+        a.policy = policy ? dev_alias(policy) + sh.lo : nullptr; a.active = active ? dev_alias(active) + sh.lo : nullptr;
+        a.flags = flags ? dev_alias(flags) + sh.lo : nullptr; a.deadline = deadline ? dev_alias(deadline) + sh.lo : nullptr;
         a.n = sh.hi - sh.lo;
-        a.last = last + sh.lo; a.next = next + sh.lo; a.missed = missed + sh.lo;
-        a.status = status + sh.lo; a.decision = decision + sh.lo;
+        a.last = dev_alias(last) + sh.lo; a.next = dev_alias(next) + sh.lo; a.missed = dev_alias(missed) + sh.lo;
+        a.status = dev_alias(status) + sh.lo; a.decision = dev_alias(decision) + sh.lo;
         CU(ctx, launch_unmet(ctx, d, d.stream, a));
         CU(ctx, collect_err(d, d.stream));
       }
@@ -627,6 +702,7 @@ extern "C" int b200cron_unmet_since(b200cron_ctx* ctx, const uint64_t* const mas
       uint8_t* d_decision = q1 + 3 * stride;
       UnmetArgs a{};
       for (int p = 0; p < 6; ++p) {
+        if (!masks[p]) { a.m.p[p] = nullptr; continue; }  // only plane 0 may be NULL (checked above): second 0
         a.m.p[p] = d_masks + p * stride;
         CU(ctx, cudaMemcpyAsync(d_masks + p * stride, masks[p] + c, cn * 8, cudaMemcpyHostToDevice, s.stream));
       }
@@ -659,10 +735,281 @@ extern "C" int b200cron_unmet_since(b200cron_ctx* ctx, const uint64_t* const mas
 }
 
 
+// test support: which Crons did the most recent b200cron_unmet_since[_dev/_set] launch on this device hand to the
+// general walk?  Copies up to `cap` of their indices (relative to that launch's arrays) to idx_host, *count = how many
+// there were.  Waits for `stream` (NULL = the context's stream) first.
+extern "C" int b200cron_debug_last_deferred(b200cron_ctx* ctx, int dev_index, void* stream, uint32_t* idx_host, size_t cap,
+                                            size_t* count) {
+  Device* d = device_at(ctx, dev_index);
+  if (!d || !count) return B200CRON_EINVAL;
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  CU(ctx, cudaSetDevice(d->id));
+  CU(ctx, cudaStreamSynchronize(stream ? (cudaStream_t)stream : d->stream));
+  *count = 0;
+  if (d->defer_last < 0) return B200CRON_OK;
+  const DeferList& b = d->defer[d->defer_last];
+  uint32_t c = 0;
+  CU(ctx, cudaMemcpy(&c, b.count, sizeof c, cudaMemcpyDeviceToHost));
+  *count = c;
+  const size_t take = std::min((size_t)c, cap);
+  if (take && idx_host) CU(ctx, cudaMemcpy(idx_host, b.idx, take * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+  return B200CRON_OK;
+}
+
+// =================================================================================================================
+// resident spec sets
+// =================================================================================================================
+// A SpecSchedule is immutable after ParseStandard (cron_controller.go:392) and a Cron's schedule only changes when its
+// CR does (api/v1alpha1/cron_types.go:77), yet the host-pointer calls above ship all 48 bytes of masks per spec on
+// every tick.  A spec set keeps the mask planes and zone ids resident in device memory, sharded over the context's
+// devices exactly as the host-pointer calls shard (shard_of); per tick only the times go in and the results come out.
+struct b200cron_specset {
+  b200cron_ctx* ctx = nullptr;
+  size_t n = 0;
+  bool have_sec = false, have_zone = false;
+  struct Part {
+    size_t lo = 0, hi = 0;
+    uint64_t* planes = nullptr;  // 6 x stride
+    int32_t* zone = nullptr;
+    size_t stride = 0;
+  };
+  std::vector<Part> parts;  // one per device of the context
+};
+
+namespace {
+
+MaskPlanes set_planes(const b200cron_specset* set, const b200cron_specset::Part& p, size_t off) {
+  MaskPlanes m;
+  for (int q = 0; q < 6; ++q) m.p[q] = (q == 0 && !set->have_sec) ? nullptr : p.planes + (size_t)q * p.stride + off;
+  return m;
+}
+
+}  // namespace
+
+extern "C" int b200cron_specset_create(b200cron_ctx* ctx, const uint64_t* const masks[6], const int32_t* zone_id,
+                                       size_t n, b200cron_specset** out) {
+  if (!ctx || !out) return B200CRON_EINVAL;
+  *out = nullptr;
+  if (!masks) return fail(ctx, B200CRON_EINVAL, "specset_create: NULL masks");
+  for (int p = 1; p < 6; ++p)
+    if (!masks[p]) return fail(ctx, B200CRON_EINVAL, "specset_create: only the seconds plane (masks[0]) may be NULL");
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  auto* set = new b200cron_specset();
+  set->ctx = ctx;
+  set->n = n;
+  set->have_sec = masks[0] != nullptr;
+  set->have_zone = zone_id != nullptr;
+  const int G = (int)ctx->devs.size();
+  set->parts.resize(G);
+  for (int g = 0; g < G; ++g) {
+    b200cron_specset::Part& p = set->parts[g];
+    const Shard sh = shard_of(n, g, G);
+    p.lo = sh.lo;
+    p.hi = sh.hi;
+    const size_t len = sh.hi > sh.lo ? sh.hi - sh.lo : 0;
+    if (len == 0) continue;
+    p.stride = align_up(len, 64);
+    cudaError_t e = cudaSetDevice(ctx->devs[g].id);
+    if (e == cudaSuccess) e = cudaMalloc(&p.planes, 6 * p.stride * sizeof(uint64_t));
+    if (e == cudaSuccess && zone_id) e = cudaMalloc(&p.zone, p.stride * sizeof(int32_t));
+    for (int q = 0; q < 6 && e == cudaSuccess; ++q)
+      if (masks[q]) e = cudaMemcpy(p.planes + (size_t)q * p.stride, masks[q] + sh.lo, len * 8, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && zone_id) e = cudaMemcpy(p.zone, zone_id + sh.lo, len * 4, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+      for (int h = 0; h <= g; ++h) {
+        cudaSetDevice(ctx->devs[h].id);
+        if (set->parts[h].planes) cudaFree(set->parts[h].planes);
+        if (set->parts[h].zone) cudaFree(set->parts[h].zone);
+      }
+      delete set;
+      return fail(ctx, e == cudaErrorMemoryAllocation ? B200CRON_ENOMEM : B200CRON_ECUDA, "specset_create: %s",
+                  cudaGetErrorString(e));
+    }
+  }
+  *out = set;
+  return B200CRON_OK;
+}
+
+extern "C" void b200cron_specset_destroy(b200cron_specset* set) {
+  if (!set) return;
+  std::lock_guard<std::mutex> lk(set->ctx->mu);
+  for (size_t g = 0; g < set->parts.size(); ++g) {
+    cudaSetDevice(set->ctx->devs[g].id);
+    if (set->parts[g].planes) cudaFree(set->parts[g].planes);
+    if (set->parts[g].zone) cudaFree(set->parts[g].zone);
+  }
+  delete set;
+}
+
+extern "C" size_t b200cron_specset_size(const b200cron_specset* set) { return set ? set->n : 0; }
+
+extern "C" int b200cron_specset_update(b200cron_specset* set, size_t first, size_t count,
+                                       const uint64_t* const masks[6], const int32_t* zone_id) {
+  if (!set) return B200CRON_EINVAL;
+  b200cron_ctx* ctx = set->ctx;
+  if (!masks || first > set->n || count > set->n - first) return fail(ctx, B200CRON_EINVAL, "specset_update: range outside the set");
+  for (int p = 0; p < 6; ++p)
+    if (!masks[p] && (p > 0 || set->have_sec))
+      return fail(ctx, B200CRON_EINVAL, "specset_update: plane %d is NULL but the set holds one", p);
+  if (set->have_zone != (zone_id != nullptr))
+    return fail(ctx, B200CRON_EINVAL, "specset_update: zone ids must be given exactly when the set was created with them");
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  for (size_t g = 0; g < set->parts.size(); ++g) {
+    const b200cron_specset::Part& p = set->parts[g];
+    const size_t lo = std::max(first, p.lo), hi = std::min(first + count, p.hi);
+    if (hi <= lo) continue;
+    Device& d = ctx->devs[g];
+    CU(ctx, cudaSetDevice(d.id));
+    // in stream order behind whatever still reads the old values on the context's stream
+    for (int q = 0; q < 6; ++q)
+      if (q > 0 || set->have_sec)
+        CU(ctx, cudaMemcpyAsync(p.planes + (size_t)q * p.stride + (lo - p.lo), masks[q] + (lo - first), (hi - lo) * 8,
+                                cudaMemcpyHostToDevice, d.stream));
+    if (zone_id)
+      CU(ctx, cudaMemcpyAsync(p.zone + (lo - p.lo), zone_id + (lo - first), (hi - lo) * 4, cudaMemcpyHostToDevice, d.stream));
+    CU(ctx, cudaStreamSynchronize(d.stream));
+  }
+  return B200CRON_OK;
+}
+
+// Next / NextN over a resident set: only `from` goes in and `out` comes back.  Pinned host buffers are used in place
+// (the kernel reads the times and writes the results over PCIe while the masks stream from HBM); pageable ones go
+// through the staged chunk pipeline.
+extern "C" int b200cron_next_n_set(b200cron_ctx* ctx, const b200cron_specset* set, const int64_t* from, int k,
+                                   int64_t* out) {
+  if (!ctx || !set || set->ctx != ctx) return B200CRON_EINVAL;
+  if (!from || !out || k < 1 || k > 64) return fail(ctx, B200CRON_EINVAL, "next_n_set: bad argument (1 <= k <= 64)");
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  const int G = (int)ctx->devs.size();
+  const bool pinned = is_pinned_host(from) && is_pinned_host(out);
+  for (int g = 0; g < G; ++g) {
+    Device& d = ctx->devs[g];
+    const b200cron_specset::Part& p = set->parts[g];
+    if (p.hi <= p.lo) continue;
+    CU(ctx, cudaSetDevice(d.id));
+    if (pinned) {
+      CU(ctx, launch_next(ctx, d, d.stream, set_planes(set, p, 0), p.zone, dev_alias(from) + p.lo, p.hi - p.lo, k,
+                          dev_alias(out) + p.lo * (size_t)k, false));
+      continue;
+    }
+    const size_t chunk = std::min(kChunk, align_up(p.hi - p.lo, 2));
+    const size_t stride = align_up(chunk, 64);
+    for (Slot& s : d.slots) {
+      int rc = ensure_slot(ctx, s, stride * (8 + (size_t)k * 8) + 1024);
+      if (rc) return rc;
+    }
+    int slot = 0;
+    for (size_t c = p.lo; c < p.hi; c += chunk, slot = (slot + 1) % kSlots) {
+      Slot& s = d.slots[slot];
+      const size_t cn = std::min(chunk, p.hi - c);
+      int64_t* d_from = reinterpret_cast<int64_t*>(s.buf);
+      int64_t* d_out = d_from + stride;
+      CU(ctx, cudaMemcpyAsync(d_from, from + c, cn * 8, cudaMemcpyHostToDevice, s.stream));
+      CU(ctx, launch_next(ctx, d, s.stream, set_planes(set, p, c - p.lo), p.zone ? p.zone + (c - p.lo) : nullptr, d_from, cn,
+                          k, d_out, true));
+      CU(ctx, cudaMemcpyAsync(out + c * (size_t)k, d_out, cn * (size_t)k * 8, cudaMemcpyDeviceToHost, s.stream));
+    }
+  }
+  for (Device& d : ctx->devs) {
+    CU(ctx, cudaSetDevice(d.id));
+    if (!pinned)
+      for (Slot& s : d.slots) CU(ctx, cudaStreamSynchronize(s.stream));
+    CU(ctx, collect_err(d, d.stream));
+    CU(ctx, cudaStreamSynchronize(d.stream));
+  }
+  return check_err_flags(ctx);
+}
+
+// getNextSchedule + gates + decision over a resident set: the per-tick arrays go in, the five result arrays come out
+extern "C" int b200cron_unmet_since_set(b200cron_ctx* ctx, const b200cron_specset* set, const int64_t* earliest,
+                                        int64_t now, int32_t now_nsec, const uint8_t* policy, const uint32_t* active,
+                                        const uint8_t* flags, const int64_t* deadline, int64_t* last, int64_t* next,
+                                        uint32_t* missed, uint8_t* status, uint8_t* decision) {
+  if (!ctx || !set || set->ctx != ctx) return B200CRON_EINVAL;
+  if (!earliest || !last || !next || !missed || !status || !decision)
+    return fail(ctx, B200CRON_EINVAL, "unmet_since_set: NULL required argument");
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  const int G = (int)ctx->devs.size();
+  const void* req[] = {earliest, last, next, missed, status, decision};
+  const void* opt[] = {policy, active, flags, deadline};
+  bool pinned = true;
+  for (const void* q : req) pinned = pinned && is_pinned_host(q);
+  for (const void* q : opt) pinned = pinned && (!q || is_pinned_host(q));
+  // staging: earliest | deadline | last | next (8 B) | active | missed (4 B) | policy flags status decision (1 B)
+  const size_t per_spec = 4 * 8 + 2 * 4 + 4;
+  for (int g = 0; g < G; ++g) {
+    Device& d = ctx->devs[g];
+    const b200cron_specset::Part& p = set->parts[g];
+    if (p.hi <= p.lo) continue;
+    CU(ctx, cudaSetDevice(d.id));
+    UnmetArgs a{};
+    a.now = now; a.now_nsec = now_nsec;
+    if (pinned) {
+      a.m = set_planes(set, p, 0);
+      a.zone_id = p.zone;
+      a.earliest = dev_alias(earliest) + p.lo;
+      a.policy = policy ? dev_alias(policy) + p.lo : nullptr; a.active = active ? dev_alias(active) + p.lo : nullptr;
+      a.flags = flags ? dev_alias(flags) + p.lo : nullptr; a.deadline = deadline ? dev_alias(deadline) + p.lo : nullptr;
+      a.n = p.hi - p.lo;
+      a.last = dev_alias(last) + p.lo; a.next = dev_alias(next) + p.lo; a.missed = dev_alias(missed) + p.lo;
+      a.status = dev_alias(status) + p.lo; a.decision = dev_alias(decision) + p.lo;
+      CU(ctx, launch_unmet(ctx, d, d.stream, a));
+      continue;
+    }
+    const size_t chunk = std::min(kChunk, align_up(p.hi - p.lo, 2));
+    const size_t stride = align_up(chunk, 64);
+    for (Slot& s : d.slots) {
+      int rc = ensure_slot(ctx, s, stride * per_spec + 1024);
+      if (rc) return rc;
+    }
+    int slot = 0;
+    for (size_t c = p.lo; c < p.hi; c += chunk, slot = (slot + 1) % kSlots) {
+      Slot& s = d.slots[slot];
+      const size_t cn = std::min(chunk, p.hi - c);
+      int64_t* d_earliest = reinterpret_cast<int64_t*>(s.buf);
+      int64_t* d_deadline = d_earliest + stride;
+      int64_t* d_last = d_deadline + stride;
+      int64_t* d_next = d_last + stride;
+      uint32_t* d_active = reinterpret_cast<uint32_t*>(d_next + stride);
+      uint32_t* d_missed = d_active + stride;
+      uint8_t* q1 = reinterpret_cast<uint8_t*>(d_missed + stride);
+      uint8_t *d_policy = q1, *d_flags = q1 + stride, *d_status = q1 + 2 * stride, *d_decision = q1 + 3 * stride;
+      CU(ctx, cudaMemcpyAsync(d_earliest, earliest + c, cn * 8, cudaMemcpyHostToDevice, s.stream));
+      if (deadline) CU(ctx, cudaMemcpyAsync(d_deadline, deadline + c, cn * 8, cudaMemcpyHostToDevice, s.stream));
+      if (active) CU(ctx, cudaMemcpyAsync(d_active, active + c, cn * 4, cudaMemcpyHostToDevice, s.stream));
+      if (policy) CU(ctx, cudaMemcpyAsync(d_policy, policy + c, cn, cudaMemcpyHostToDevice, s.stream));
+      if (flags) CU(ctx, cudaMemcpyAsync(d_flags, flags + c, cn, cudaMemcpyHostToDevice, s.stream));
+      a.m = set_planes(set, p, c - p.lo);
+      a.zone_id = p.zone ? p.zone + (c - p.lo) : nullptr;
+      a.earliest = d_earliest;
+      a.policy = policy ? d_policy : nullptr; a.active = active ? d_active : nullptr;
+      a.flags = flags ? d_flags : nullptr; a.deadline = deadline ? d_deadline : nullptr;
+      a.n = cn; a.last = d_last; a.next = d_next; a.missed = d_missed; a.status = d_status; a.decision = d_decision;
+      CU(ctx, launch_unmet(ctx, d, s.stream, a));
+      CU(ctx, cudaMemcpyAsync(last + c, d_last, cn * 8, cudaMemcpyDeviceToHost, s.stream));
+      CU(ctx, cudaMemcpyAsync(next + c, d_next, cn * 8, cudaMemcpyDeviceToHost, s.stream));
+      CU(ctx, cudaMemcpyAsync(missed + c, d_missed, cn * 4, cudaMemcpyDeviceToHost, s.stream));
+      CU(ctx, cudaMemcpyAsync(status + c, d_status, cn, cudaMemcpyDeviceToHost, s.stream));
+      CU(ctx, cudaMemcpyAsync(decision + c, d_decision, cn, cudaMemcpyDeviceToHost, s.stream));
+    }
+  }
+  for (Device& d : ctx->devs) {
+    CU(ctx, cudaSetDevice(d.id));
+    if (!pinned)
+      for (Slot& s : d.slots) CU(ctx, cudaStreamSynchronize(s.stream));
+    CU(ctx, collect_err(d, d.stream));
+    CU(ctx, cudaStreamSynchronize(d.stream));
+  }
+  return check_err_flags(ctx);
+}
+
 // =================================================================================================================
 // unmet list
 // =================================================================================================================
 namespace {
+
+// per-Cron list lengths are summed in 32 bits inside a tile of kScanTile Crons: cap <= 2^20 keeps a tile below 2^30
+constexpr uint32_t kListCapMax = 1u << 20;
 
 int launch_list_offsets(b200cron_ctx* ctx, Device& d, cudaStream_t st, const uint32_t* missed, const uint8_t* decision,
                         size_t n, uint32_t cap, uint64_t* list_off, uint64_t* tile_sums) {
@@ -693,6 +1040,7 @@ extern "C" int b200cron_unmet_list_offsets_dev(b200cron_ctx* ctx, int dev_index,
   Device* d = device_at(ctx, dev_index);
   if (!d) return B200CRON_EINVAL;
   if (!missed || !decision || !list_off) return fail(ctx, B200CRON_EINVAL, "unmet_list_offsets: NULL argument");
+  if (cap > kListCapMax) return fail(ctx, B200CRON_EINVAL, "unmet_list_offsets: cap = %u exceeds %u", cap, kListCapMax);
   std::lock_guard<std::mutex> lk(ctx->mu);
   CU(ctx, cudaSetDevice(d->id));
   cudaStream_t st = stream ? (cudaStream_t)stream : d->stream;
@@ -735,6 +1083,7 @@ extern "C" int b200cron_unmet_list_offsets_static(b200cron_ctx* ctx, int dev_ind
   Device* d = device_at(ctx, dev_index);
   if (!d) return B200CRON_EINVAL;
   if (!missed || !decision || !list_off) return fail(ctx, B200CRON_EINVAL, "unmet_list_offsets_static: NULL argument");
+  if (cap > kListCapMax) return fail(ctx, B200CRON_EINVAL, "unmet_list_offsets_static: cap = %u exceeds %u", cap, kListCapMax);
   if (n > kStaticMaxN)
     return fail(ctx, B200CRON_EINVAL,
                 "unmet_list_offsets_static: n = %zu exceeds the fixed scratch (at most %zu Crons per call); split the "
@@ -766,6 +1115,8 @@ extern "C" int b200cron_unmet_list_emit_dev(b200cron_ctx* ctx, int dev_index, vo
   Device* d = device_at(ctx, dev_index);
   if (!d) return B200CRON_EINVAL;
   if (!masks || !earliest || !list_off) return fail(ctx, B200CRON_EINVAL, "unmet_list_emit: NULL argument");
+  for (int p = 1; p < 6; ++p)
+    if (!masks[p]) return fail(ctx, B200CRON_EINVAL, "unmet_list_emit: only the seconds plane (masks[0]) may be NULL");
   if (n == 0) return B200CRON_OK;
   std::lock_guard<std::mutex> lk(ctx->mu);
   CU(ctx, cudaSetDevice(d->id));
@@ -784,6 +1135,9 @@ extern "C" int b200cron_unmet_list(b200cron_ctx* ctx, const uint64_t* const mask
   if (!ctx) return B200CRON_EINVAL;
   if (!masks || !earliest || !missed || !decision || !list_off)
     return fail(ctx, B200CRON_EINVAL, "unmet_list: NULL required argument");
+  for (int p = 1; p < 6; ++p)
+    if (!masks[p]) return fail(ctx, B200CRON_EINVAL, "unmet_list: only the seconds plane (masks[0]) may be NULL");
+  if (cap > kListCapMax) return fail(ctx, B200CRON_EINVAL, "unmet_list: cap = %u exceeds %u", cap, kListCapMax);
   if (n == 0) { list_off[0] = 0; return B200CRON_OK; }
   std::lock_guard<std::mutex> lk(ctx->mu);
   Device& d = ctx->devs[0];
@@ -804,6 +1158,7 @@ extern "C" int b200cron_unmet_list(b200cron_ctx* ctx, const uint64_t* const mask
   uint8_t* d_decision = reinterpret_cast<uint8_t*>(d_missed + stride);
   MaskPlanes m;
   for (int p = 0; p < 6; ++p) {
+    if (!masks[p]) { m.p[p] = nullptr; continue; }  // only plane 0 may be NULL (checked above): second 0
     m.p[p] = d_masks + p * stride;
     CU(ctx, cudaMemcpyAsync(d_masks + p * stride, masks[p], n * 8, cudaMemcpyHostToDevice, s.stream));
   }

@@ -29,17 +29,6 @@
 #define CW_LDG(p) (*(p))
 #endif
 
-#ifndef B200CRON_WALK_DAY_PLAIN
-// 1: chained calls that stay on a day lying wholly inside one zone period skip the closed form's prerequisites (see
-// Walk::day_plain).  Opt-in: verified against the oracle on the host build, not yet timed on a GPU.
-#define B200CRON_WALK_DAY_PLAIN 0
-#endif
-#if B200CRON_WALK_DAY_PLAIN
-#define CW_DAY_PLAIN(stmt) stmt
-#else
-#define CW_DAY_PLAIN(stmt)
-#endif
-
 #ifndef CW_TRACE
 #define CW_TRACE(tag, w)
 #endif
@@ -53,6 +42,8 @@ constexpr int64_t kZero = INT64_MIN;  // Go's time.Time{} at every boundary of t
 constexpr int64_t kAlpha = INT64_MIN;
 constexpr int64_t kOmega = INT64_MAX;
 constexpr int32_t kStuck = 400;  // iterations of one loop entry no terminating upstream walk can reach
+constexpr int64_t kYearBase = -2208988800LL;  // 1900-01-01T00:00:00Z: origin of the zone table's year index
+constexpr uint32_t kYearStep128 = 246375u;    // bucket width of 365 days, in units of 128 seconds
 
 // Flattened zone table in HBM (L2-resident: ~0.5 MB for all IANA zones).  Zone z owns entries
 // [zstart[z], zstart[z+1]); entry i is in force for when[i] <= sec < when[i+1] (when of the first entry is kAlpha,
@@ -62,16 +53,24 @@ struct ZoneTable {
   const int32_t* off;
   const int32_t* fpre;  // per zone: running count of transitions whose gap/overlap contains a local midnight
   const int32_t* zstart;
+  const uint16_t* yidx;  // year index: row z = period in force at the start of every 365-day bucket since 1900 (zone_table.h)
+  int32_t ystride;       // entries per row (buckets + 1)
   int32_t nzones;
   int64_t horizon;  // zoned inputs must be < horizon - 6 years (checked by the caller of the kernels)
 };
 
+// A ConstantDelaySchedule (robfig constantdelay.go; what ParseStandard returns for "@every <dur>", reached by the
+// reference at cron_controller.go:392,405,409,436) travels in the same six planes: month == kEveryTag (a bit no
+// parser sets) marks it, dom holds Delay in whole seconds, the other planes are ignored.
+constexpr uint64_t kEveryTag = 1ULL << 62;
+
 struct Spec {  // sanitised masks: only the bits upstream can test are kept
-  uint64_t second, minute;
+  uint64_t second, minute;  // every: `second` holds the delay in seconds (>= 1) instead of a mask
   uint32_t hour, dom, month, dow;
   uint32_t month_eff;  // month mask minus the months that can never hold a matching day (closed form only)
   bool star;   // Dom&starBit || Dow&starBit  -> AND rule, else OR rule (spec.go dayMatches)
   bool never;  // some field can never match: upstream walks to the 5-year limit and returns the zero time
+  bool every;  // ConstantDelaySchedule: Next(t) = t + delay; `never` is set too, so no walk ever starts on it
   int32_t tod1;     // first matching second of day (first hour, first minute, first second); valid when !never
   int32_t first_ms; // first matching minute * 60 + first matching second
   int32_t first_s;  // first matching second
@@ -105,6 +104,11 @@ CW_HD Spec make_spec(uint64_t second, uint64_t minute, uint64_t hour, uint64_t d
   s.first_s = fs;
   s.first_ms = fm * 60 + fs;
   s.tod1 = fh * 3600 + s.first_ms;
+  s.every = month == kEveryTag;
+  if (s.every) {  // constantdelay.go Every() never builds a delay below one second; clamp a hand-built plane likewise
+    s.never = true;
+    s.second = (int64_t)dom < 1 ? 1ULL : dom;
+  }
   return s;
 }
 
@@ -204,7 +208,9 @@ struct Walk {
   const int64_t* zw;   // this zone's `when` entries
   const int32_t* zo;   // this zone's offsets
   const int32_t* zf;   // this zone's midnight-transition prefix counts
+  const uint16_t* zy;  // this zone's row of the year index
   int32_t zn;          // entry count (1 for UTC / fixed zones)
+  int32_t ynb;         // buckets in the row
   // cached period holding the last looked-up instant
   int32_t pidx;
   int32_t off;
@@ -216,11 +222,6 @@ struct Walk {
   int32_t sod;  // local second of day
   int32_t Y, M, D;
   bool today_ok;  // the resident day is known to satisfy the month and day masks (set when a fire was found on it)
-#if B200CRON_WALK_DAY_PLAIN
-  // today_ok, and the resident local day is natural from end to end and ends inside the cached period (whole-minute
-  // offset): every later fire of this day is then "next matching time of day", with nothing else to check
-  bool day_plain;
-#endif
   // chained calls (NextN): day mask of the resident month, and the day's last matching second (86400 = not set)
   uint32_t dm_month;
   bool dm_ok;
@@ -232,15 +233,14 @@ struct Walk {
     nhi = (pe == kOmega) ? kOmega : pe + (off < 0 ? off : 0);
   }
   CW_HD void bind_utc() {
-    zw = nullptr; zo = nullptr; zf = nullptr; zn = 1; pidx = 0; off = 0; ps = kAlpha; pe = kOmega; nlo = kAlpha; nhi = kOmega; today_ok = false; dm_ok = false; dm_month = 0; tod_last = 86400;
-    CW_DAY_PLAIN(day_plain = false;)
+    zw = nullptr; zo = nullptr; zf = nullptr; zy = nullptr; ynb = 0; zn = 1; pidx = 0; off = 0; ps = kAlpha; pe = kOmega; nlo = kAlpha; nhi = kOmega; today_ok = false; dm_ok = false; dm_month = 0; tod_last = 86400;
   }
   CW_HD void bind_zone(const ZoneTable& zt, int32_t zone) {
     const int32_t a = CW_LDG(zt.zstart + zone), b = CW_LDG(zt.zstart + zone + 1);
     zw = zt.when + a; zo = zt.off + a; zf = zt.fpre + a; zn = b - a;
+    zy = zt.yidx + (size_t)zone * (size_t)zt.ystride; ynb = zt.ystride - 1;
     pidx = -1; off = 0; ps = 1; pe = 0; nlo = 1; nhi = 0;  // empty cache
     today_ok = false; dm_ok = false; dm_month = 0; tod_last = 86400;
-    CW_DAY_PLAIN(day_plain = false;)
     if (zn == 1) { pidx = 0; off = CW_LDG(zo); ps = kAlpha; pe = kOmega; nlo = kAlpha; nhi = kOmega; }
   }
 
@@ -252,12 +252,20 @@ struct Walk {
       if (x >= pe) { lo = pidx + 1; if (lo + 1 >= zn || x < CW_LDG(zw + lo + 1)) hi = lo + 1; }
       else { hi = pidx; if (hi - 1 >= 0 && x >= CW_LDG(zw + hi - 1)) lo = hi - 1; }
     }
+    if (hi - lo > 1 && x >= kYearBase) {
+      // year index: the period in force at the start of x's 365-day bucket and of the next bucket bracket the answer
+      const uint32_t b = (uint32_t)((uint64_t)(x - kYearBase) >> 7) / kYearStep128;
+      if (b < (uint32_t)ynb) {
+        const int32_t l2 = (int32_t)CW_LDG(zy + b), h2 = (int32_t)CW_LDG(zy + b + 1) + 1;
+        lo = lo > l2 ? lo : l2;
+        hi = hi < h2 ? hi : h2;
+      }
+    }
     while (hi - lo > 1) {
       const int32_t mid = (int32_t)((uint32_t)(lo + hi) >> 1);
       if (x < CW_LDG(zw + mid)) hi = mid; else lo = mid;
     }
     pidx = lo;
-    CW_DAY_PLAIN(day_plain = false;)
     off = CW_LDG(zo + lo);
     ps = CW_LDG(zw + lo);
     pe = (lo + 1 < zn) ? CW_LDG(zw + lo + 1) : kOmega;
@@ -283,17 +291,9 @@ struct Walk {
     sod = r * 128 + (int32_t)(l & 127);
     civil_from_days(dn, Y, M, D);
     today_ok = false;
-    CW_DAY_PLAIN(day_plain = false;)
     dm_ok = false;
   }
 
-#if B200CRON_WALK_DAY_PLAIN
-  // call with the walk on a fire time whose day matched (today_ok) and the period cache on that fire
-  CW_HD void mark_day_plain() {
-    day_plain = (off % 60 == 0) && t >= ps && nlo <= (int64_t)dn * 86400 && (int64_t)(dn + 1) * 86400 <= nhi &&
-                (pe == kOmega || t + (86400 - sod) <= pe);
-  }
-#endif
   // load() for a walk bound to UTC: no period lookup
   CW_HD void load_utc(int64_t tt) {
     t = tt;
@@ -305,7 +305,6 @@ struct Walk {
     sod = r * 128 + (int32_t)(tt & 127);
     civil_from_days(dn, Y, M, D);
     today_ok = false;
-    CW_DAY_PLAIN(day_plain = false;)
     dm_ok = false;
   }
 
@@ -346,7 +345,6 @@ struct Walk {
   // move the resident fields forward by k whole days inside the same period (k >= 1, small)
   CW_HD void advance_days(int32_t k) {
     today_ok = false;
-    CW_DAY_PLAIN(day_plain = false;)
     dm_ok = false;
     dn += k;
     D += k;
@@ -645,7 +643,6 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
       if (kUtcOnly || (w.t + (86400 - sod) < w.pe && w.natural(x1) && w.natural(xk) && r < w.pe)) {
         w.t = r;
         w.dn += k; w.D = Dn; w.sod = s.tod1;
-        CW_DAY_PLAIN(w.mark_day_plain();)
         *out = r;
         return true;
       }
@@ -676,7 +673,6 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
         w.t = r;
         w.sod = rsod;
         w.today_ok = true;
-        CW_DAY_PLAIN(w.mark_day_plain();)
         if (have_dm) { w.dm_month = dm; w.dm_ok = true; }
         *out = r;
         return true;
@@ -733,7 +729,6 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
     w.t = x_mid + s.tod1 - (kUtcOnly ? 0 : w.off);
     w.dn = found_dn; w.sod = s.tod1; w.Y = Yc; w.M = Mc; w.D = Dc;
     w.today_ok = true;
-    CW_DAY_PLAIN(w.mark_day_plain();)
     w.dm_month = dm_found; w.dm_ok = true;
     *out = w.t;
     return true;
@@ -768,7 +763,6 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
   w.t = r;
   w.dn = found_dn; w.sod = rsod; w.Y = Yc; w.M = Mc; w.D = Dc;
   w.today_ok = true;
-  CW_DAY_PLAIN(w.mark_day_plain();)
   w.dm_month = dm_found; w.dm_ok = true;
   *out = r;
   return true;
@@ -780,18 +774,7 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
 template <bool kUtcOnly = false>
 CW_HD bool next_try(const Spec& s, Walk& w, int64_t t, bool resident, int64_t* out) {
   CW_COUNT(next);
-  if (s.never) { *out = kZero; return true; }
-#if B200CRON_WALK_DAY_PLAIN
-  if (resident && w.day_plain && w.sod + 1 < 86400) {
-    const int32_t tod = next_tod_ge(s, w.sod + 1);
-    if (tod >= 0) {
-      w.t += tod - w.sod;
-      w.sod = tod;
-      *out = w.t;
-      return true;
-    }
-  }
-#endif
+  if (s.never) { *out = s.every ? t + (int64_t)s.second : kZero; return true; }  // constantdelay.go Next: t.Add(Delay)
   const int64_t t1 = t + 1;
   if (resident && (kUtcOnly || t1 < w.pe) && w.sod + 1 < 86400) {
     w.t = t1;
@@ -821,7 +804,6 @@ SlowResult walk_next_outlined(Spec s, Walk w) {
   x.w.lookup(x.w.t);  // fast_next may have moved the period cache; the step emulation wants it on t
   x.r = walk_next(s, x.w);
   x.w.today_ok = false;  // the emulation can end on a day upstream never re-checked
-  CW_DAY_PLAIN(x.w.day_plain = false;)
   x.w.dm_ok = false;
   return x;
 }
@@ -838,7 +820,6 @@ CW_HD int64_t next_slow(const Spec& s, Walk& w) {
   w.lookup(w.t);
   const int64_t r = walk_next(s, w);
   w.today_ok = false;
-  CW_DAY_PLAIN(w.day_plain = false;)
   w.dm_ok = false;
   return r;
 }

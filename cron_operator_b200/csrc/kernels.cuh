@@ -49,7 +49,7 @@ __device__ __forceinline__ bool bind_checked(Walk& w, const ZoneTable& zt, int32
 // Algorithmic bytes: 48 (masks) + 8 (from) [+ 4 zone] in, 8k out per spec.
 // -------------------------------------------------------------------------------------------------------------
 #ifndef B200CRON_NEXTN_STAGE
-#define B200CRON_NEXTN_STAGE 1  // 0: results go straight to global memory, no shared-memory staging (tuning)
+#define B200CRON_NEXTN_STAGE 0  // 1: stage results in shared memory and write full rows (measured 6 % slower on C3)
 #endif
 #ifndef B200CRON_NEXTN_MINBLOCKS
 #define B200CRON_NEXTN_MINBLOCKS 12
@@ -126,7 +126,7 @@ next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* 
       if (ok && t != kZero) {
         t = cronwalk::next_from(ss, w, t, j > 0);
         // chained calls keep walking: re-check the zoned horizon (UTC never trips it)
-        if (KT != 1 && t != kZero && w.zn > 1 && t >= zt.horizon - kSixYears) { atomicOr(err, kErrRange); ok = false; t = kZero; }
+        if (KT != 1 && t != kZero && !ss.every && w.zn > 1 && t >= zt.horizon - kSixYears) { atomicOr(err, kErrRange); ok = false; t = kZero; }
       } else {
         t = kZero;
       }
@@ -166,6 +166,81 @@ next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* 
 
 
 // -------------------------------------------------------------------------------------------------------------
+// next_n over class-pure warps (k > 1 with zone ids).  In input order half of a C3 warp's lanes are UTC and ride
+// through the zoned instruction stream (zone prerequisites, period lookups, the step emulation), and the kernel sits at
+// 80 registers for everybody.  Here a CTA takes a tile of kNextTileSpecs consecutive specs, deals the indices of ONE
+// class -- evaluated in UTC (kUtc) or in a zone -- into shared memory with a ballot compaction and walks only those, in
+// dense warps; the host launches the kernel once per class.  The UTC instantiation has no zone logic and no step
+// emulation in its instruction stream (in UTC the closed form always answers) and half the registers, so twice the
+// resident warps.  Loads are gathers inside the tile (every sector is used by one class or the other; the second
+// launch finds most of them in L2), results go straight to the spec's row (the pattern B200CRON_NEXTN_STAGE=0 measured
+// best).  A launch without zone ids is all UTC: no classification.
+// -------------------------------------------------------------------------------------------------------------
+constexpr int kNextTileThreads = 128;
+constexpr int kNextTileSpecs = 512;
+#ifndef B200CRON_NEXTN_UTC_MINBLOCKS
+#define B200CRON_NEXTN_UTC_MINBLOCKS 10
+#endif
+#ifndef B200CRON_NEXTN_ZONED_MINBLOCKS
+#define B200CRON_NEXTN_ZONED_MINBLOCKS 6
+#endif
+
+template <int KT, bool kUtc>
+__global__ void __launch_bounds__(kNextTileThreads, kUtc ? B200CRON_NEXTN_UTC_MINBLOCKS : B200CRON_NEXTN_ZONED_MINBLOCKS)
+next_n_tile_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* __restrict__ from, size_t n, int k_rt,
+                   int64_t* __restrict__ out, ZoneTable zt, int* __restrict__ err) {
+  __shared__ uint16_t s_idx[kNextTileSpecs];
+  __shared__ int s_n;
+  const int k = KT > 0 ? KT : k_rt;
+  const size_t base = (size_t)blockIdx.x * kNextTileSpecs;
+  const int cnt = (int)((n - base) < (size_t)kNextTileSpecs ? (n - base) : (size_t)kNextTileSpecs);
+  const unsigned lane = threadIdx.x & 31u;
+  int mine = cnt;
+  if (zone_id != nullptr) {
+    if (threadIdx.x == 0) s_n = 0;
+    __syncthreads();
+#pragma unroll
+    for (int it = 0; it < kNextTileSpecs / kNextTileThreads; ++it) {
+      const int q = it * kNextTileThreads + threadIdx.x;
+      const bool take = q < cnt && ((__ldg(zone_id + base + q) == 0) == kUtc);
+      const unsigned mk = __ballot_sync(0xffffffffu, take);
+      int b = 0;
+      if (lane == 0 && mk) b = atomicAdd(&s_n, __popc(mk));
+      b = __shfl_sync(0xffffffffu, b, 0);
+      if (take) s_idx[b + __popc(mk & ((1u << lane) - 1u))] = (uint16_t)q;
+    }
+    __syncthreads();
+    mine = s_n;
+  } else if (!kUtc) {
+    return;  // no zone ids: nothing is zoned
+  }
+  for (int q = threadIdx.x; q < ((mine + 31) & ~31); q += kNextTileThreads) {
+    const bool live = q < mine;
+    const size_t i = base + (live ? (zone_id ? (int)s_idx[q] : q) : 0);
+    const Spec ss = cronwalk::make_spec(m.p[0] ? __ldg(m.p[0] + i) : 1ULL, __ldg(m.p[1] + i), __ldg(m.p[2] + i),
+                                        __ldg(m.p[3] + i), __ldg(m.p[4] + i), __ldg(m.p[5] + i));
+    int64_t t = __ldg(from + i);
+    const int32_t zone = kUtc ? 0 : __ldg(zone_id + i);
+    Walk w;
+    bool ok = live && bind_checked(w, zt, zone, t, err);
+    if (!live) w.bind_utc();
+    if (!ss.never) w.tod_last = cronwalk::spec_tod_last(ss);  // lets chained calls skip exhausted days
+    int64_t* row = out + i * (size_t)k;
+#pragma unroll 1
+    for (int j = 0; j < k; ++j) {
+      __syncwarp();  // every lane runs exactly k iterations: re-converge, or lanes on a short path run ahead for good
+      if (ok && t != kZero) {
+        t = cronwalk::next_from_t<false, kUtc>(ss, w, t, j > 0);
+        if (!kUtc && t != kZero && !ss.every && w.zn > 1 && t >= zt.horizon - kSixYears) { atomicOr(err, kErrRange); ok = false; t = kZero; }
+      } else {
+        t = kZero;
+      }
+      if (live) row[j] = t;
+    }
+  }
+}
+
+// -------------------------------------------------------------------------------------------------------------
 // next1: the k == 1 case with ONE spec per lane (64-bit loads, still 256 contiguous bytes per plane per warp).
 // A 1M-spec launch is only ~30 us long: with two specs per lane a resident warp gets ~4.4 tiles and the last,
 // partly filled wave leaves SMs idle for ~20 % of the kernel; halving the tile halves that quantisation loss,
@@ -188,14 +263,143 @@ next1_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* _
   // has got this far, instead of idling through this launch's last partial wave.  A no-op for ordinary launches.
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const size_t i = (size_t)blockIdx.x * kNext1Threads + threadIdx.x;
-  if (i >= n) return;
+  if (i >= n) { asm volatile("griddepcontrol.wait;" ::: "memory"); return; }
   const Spec s = cronwalk::make_spec(m.p[0] ? __ldg(m.p[0] + i) : 1ULL, __ldg(m.p[1] + i), __ldg(m.p[2] + i), __ldg(m.p[3] + i),
                                      __ldg(m.p[4] + i), __ldg(m.p[5] + i));
   const int64_t t = __ldg(from + i);
   const int32_t zone = (!kUtcOnly && zone_id) ? __ldg(zone_id + i) : 0;
   Walk w;
   const bool ok = bind_checked(w, zt, zone, t, err);
-  out[i] = ok ? cronwalk::next_from_t<false, kUtcOnly>(s, w, t, false) : kZero;
+  const int64_t r = ok ? cronwalk::next_from_t<false, kUtcOnly>(s, w, t, false) : kZero;
+  // The other half of the programmatic launch: wait for the launch this one may have overlapped to complete (and
+  // flush) before publishing anything.  Completion is then transitive along the stream -- when this grid has
+  // finished, so has every earlier one -- which is what later stream work (copies, event records, other kernels)
+  // relies on.  Returns at once for a launch that overlapped nothing.
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  out[i] = r;
+}
+
+// -------------------------------------------------------------------------------------------------------------
+// next1 with persistent warps and an asynchronous input ring (the default for k == 1 on device-resident inputs).
+//
+// next1_kernel gives every warp one tile: issue seven loads, wait a DRAM round trip, walk, store, exit -- the wait is
+// the kernel's top stall, and a 1M-spec launch ends in a ragged last wave.  Here the grid is sized to the machine
+// (resident CTAs only) and every warp walks a strided sequence of 32-spec tiles.  A warp owns kRingStages stages of
+// shared memory (7 planes x 256 B + 128 B of zone ids each) and one mbarrier per stage; lane 0 fills a stage with 1-D
+// bulk async copies (cp.async.bulk, one per plane, completion counted in bytes on the stage's mbarrier), so the loads of
+// tile i+2 are in flight while tile i is walked and a warp never waits for DRAM after its first tile.  Warps do not
+// synchronise with each other at all: stage reuse is ordered by __syncwarp (the warp is the stage's only reader).
+// Bulk copies read THIS GPU's global memory only (the host passes device-resident buffers; pinned host buffers take
+// next1_kernel).  The n % 32 leftover specs are walked by warp 0 with plain loads.
+// -------------------------------------------------------------------------------------------------------------
+#ifndef B200CRON_RING_STAGES
+#define B200CRON_RING_STAGES 2
+#endif
+#ifndef B200CRON_RING_MINBLOCKS
+#define B200CRON_RING_MINBLOCKS 12
+#endif
+constexpr int kRingThreads = 128;
+constexpr int kRingWarps = kRingThreads / 32;
+constexpr int kRingStages = B200CRON_RING_STAGES;
+constexpr int kRingStageBytes = 7 * 256 + 128;  // six mask planes + from (32 x 8 B each), zone ids (32 x 4 B)
+constexpr int kRingSmemBytes = kRingWarps * kRingStages * kRingStageBytes + kRingWarps * kRingStages * 8;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra WAIT_DONE;\n"
+      "bra WAIT_LOOP;\n"
+      "WAIT_DONE:\n"
+      "}\n" ::"r"(bar), "r"(parity) : "memory");
+}
+// 1-D bulk copy global -> this CTA's shared memory, completion signalled on `bar` in bytes
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+
+template <bool kUtcOnly>
+__global__ void __launch_bounds__(kRingThreads, B200CRON_RING_MINBLOCKS)
+next1_ring_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* __restrict__ from, size_t n,
+                  int64_t* __restrict__ out, ZoneTable zt, int* __restrict__ err) {
+  extern __shared__ __align__(128) unsigned char ring_smem[];
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");  // see next1_kernel
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  unsigned char* my = ring_smem + (size_t)warp * kRingStages * kRingStageBytes;
+  const uint32_t my_u32 = smem_u32(my);
+  const uint32_t bar0 = smem_u32(ring_smem + kRingWarps * kRingStages * kRingStageBytes) + (uint32_t)warp * kRingStages * 8u;
+  const bool have_sec = m.p[0] != nullptr;
+  const bool have_zone = !kUtcOnly && zone_id != nullptr;
+  const uint32_t stage_tx = (have_sec ? 7u : 6u) * 256u + (have_zone ? 128u : 0u);
+  const size_t tiles = n / 32;                                   // full tiles; the rest is the tail below
+  const size_t W = (size_t)gridDim.x * kRingWarps;               // warps in the grid
+  const size_t g = (size_t)blockIdx.x + (size_t)gridDim.x * warp;  // consecutive tiles go to different CTAs
+  if (lane == 0) {
+#pragma unroll
+    for (int st = 0; st < kRingStages; ++st) mbar_init(bar0 + 8u * st, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncwarp();
+  auto fill = [&](size_t tile, int st) {  // lane 0 only
+    const uint32_t dst = my_u32 + (uint32_t)st * kRingStageBytes, bar = bar0 + 8u * st;
+    const size_t e = tile * 32;
+    mbar_expect_tx(bar, stage_tx);
+#pragma unroll
+    for (int p = 1; p < 6; ++p) bulk_g2s(dst + p * 256, m.p[p] + e, 256, bar);
+    if (have_sec) bulk_g2s(dst, m.p[0] + e, 256, bar);
+    bulk_g2s(dst + 6 * 256, from + e, 256, bar);
+    if (have_zone) bulk_g2s(dst + 7 * 256, zone_id + e, 128, bar);
+  };
+  if (lane == 0) {
+#pragma unroll
+    for (int st = 0; st < kRingStages; ++st)
+      if (g + (size_t)st * W < tiles) fill(g + (size_t)st * W, st);
+  }
+  bool waited = false;
+  int st = 0;
+  uint32_t parity = 0;
+  for (size_t tile = g; tile < tiles; tile += W) {
+    mbar_wait(bar0 + 8u * st, parity);
+    const unsigned char* sp = my + st * kRingStageBytes;
+    const uint64_t* pl = reinterpret_cast<const uint64_t*>(sp) + lane;
+    const Spec s = cronwalk::make_spec(have_sec ? pl[0] : 1ULL, pl[32], pl[64], pl[96], pl[128], pl[160]);
+    const int64_t t = (int64_t)pl[192];
+    const int32_t zone = have_zone ? reinterpret_cast<const int32_t*>(sp + 7 * 256)[lane] : 0;
+    __syncwarp();  // every lane has taken its operands out of the stage: lane 0 may refill it
+    if (lane == 0 && tile + (size_t)kRingStages * W < tiles) fill(tile + (size_t)kRingStages * W, st);
+    if (++st == kRingStages) { st = 0; parity ^= 1u; }
+    Walk w;
+    const bool ok = bind_checked(w, zt, zone, t, err);
+    const int64_t r = ok ? cronwalk::next_from_t<false, kUtcOnly>(s, w, t, false) : kZero;
+    if (!waited) { asm volatile("griddepcontrol.wait;" ::: "memory"); waited = true; }  // see next1_kernel
+    out[tile * 32 + lane] = r;
+  }
+  if (g == 0) {  // the n % 32 leftover specs
+    const size_t i = tiles * 32 + lane;
+    if (i < n) {
+      const Spec s = cronwalk::make_spec(have_sec ? __ldg(m.p[0] + i) : 1ULL, __ldg(m.p[1] + i), __ldg(m.p[2] + i),
+                                         __ldg(m.p[3] + i), __ldg(m.p[4] + i), __ldg(m.p[5] + i));
+      const int64_t t = __ldg(from + i);
+      const int32_t zone = have_zone ? __ldg(zone_id + i) : 0;
+      Walk w;
+      const bool ok = bind_checked(w, zt, zone, t, err);
+      const int64_t r = ok ? cronwalk::next_from_t<false, kUtcOnly>(s, w, t, false) : kZero;
+      if (!waited) { asm volatile("griddepcontrol.wait;" ::: "memory"); waited = true; }
+      out[i] = r;
+    }
+  }
+  if (!waited) asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
 // -------------------------------------------------------------------------------------------------------------
@@ -223,18 +427,23 @@ struct UnmetArgs {
   uint8_t* decision;
 };
 
-// 12 CTAs/SM (40 registers, some spills): the kernel is bound by instruction-fetch redirects in branchy, divergent
-// code (ncu: 21 % issue-active at 24 warps/SM); more resident warps hide them -- measured 8.3 -> 6.9 ms per 10M Crons.
-//
-// Modes.  kUnmetSingle: one launch does everything.  kUnmetEasy + kUnmetHard (the default pair): the easy kernel lets
-// only the closed form answer, gives every Cron at most kUnmetEasyRounds rounds (first fire + fast-forward, a zone
-// transition crossed + fast-forward, ..., end of chain, Next(now)) and appends the Crons that need more -- a step only
-// the emulation can take, a backward step -- to a compact index list; the hard kernel then runs the general state
-// machine over that list only, in dense warps.  On the C4 workload (10M Crons, B200) 3 rounds defer 8 % of the Crons
-// and take 5.23 ms, 4 rounds 4.6 % / 4.79 ms, 5 rounds 2.4 % / 4.34 ms, 6 rounds the same 2.4 % / 4.35 ms: what is
-// left after five rounds needs the step emulation, which in the single kernel (7.30 ms) made every second warp run it
-// for one or two lanes.  The easy kernel has no step emulation in its instruction stream.
-enum { kUnmetSingle = 0, kUnmetEasy = 1, kUnmetHard = 2 };
+// The unmet path runs as up to three kinds of launch (plans in launch_unmet, b200cron.cu):
+//   unmet_tile_kernel   walks the Crons in input order, a tile of kUnmetTile per CTA.  Inside the tile the Crons are
+//                       first dealt into two classes -- evaluated in UTC / evaluated in a zone -- with a ballot
+//                       compaction in shared memory, so that warps are class-pure: UTC warps run unmet_step_utc (no zone
+//                       logic, no step emulation, nothing to defer: ~5x fewer instructions), zoned warps run the easy
+//                       rounds below.  On C4 half of the Crons are UTC and, mixed into every warp in input order, they
+//                       used to ride through the whole zoned instruction stream.
+//   unmet_ordered_kernel the easy rounds over an index list grouped by zone id (zone_order_* kernels): a warp's 32
+//                       Crons then share their zone's periods and transition, and the zone-dependent code stops
+//                       diverging.  Used for the zoned class when the plan says so (the tile kernel then only does UTC).
+//   unmet_hard_kernel   the general state machine (with the step emulation) over the compact list of Crons the easy
+//                       rounds gave up on, in dense warps.
+// Easy rounds: only the closed form may answer, at most kUnmetEasyRounds rounds per Cron (first fire + fast-forward, a
+// zone transition crossed + fast-forward, ..., end of chain, Next(now)); a Cron that needs more -- a step only the
+// emulation can take, a backward step -- is appended (ballot + one atomic per warp) to the defer list.  On C4 five
+// rounds defer 2.4 % of the Crons (all in zones whose transitions sit on local midnight).
+enum { kUnmetSingle = 0, kUnmetEasy = 1, kUnmetHard = 2, kUnmetUtc = 3 };
 #ifndef B200CRON_UNMET_EASY_ROUNDS
 #define B200CRON_UNMET_EASY_ROUNDS 5
 #endif
@@ -252,7 +461,8 @@ __device__ __forceinline__ void unmet_one(const UnmetArgs& a, const ZoneTable& z
                                           bool live, uint32_t* __restrict__ defer_idx,
                                           uint32_t* __restrict__ defer_count) {
   const size_t ii = live ? i : 0;  // out-of-range lanes stay in the warp-uniform loop below, doing nothing
-  const Spec s = cronwalk::make_spec(__ldg(a.m.p[0] + ii), __ldg(a.m.p[1] + ii), __ldg(a.m.p[2] + ii),
+  // masks[0] == NULL: 5-field schedules, second 0 (what ParseStandard always yields)
+  const Spec s = cronwalk::make_spec(a.m.p[0] ? __ldg(a.m.p[0] + ii) : 1ULL, __ldg(a.m.p[1] + ii), __ldg(a.m.p[2] + ii),
                                      __ldg(a.m.p[3] + ii), __ldg(a.m.p[4] + ii), __ldg(a.m.p[5] + ii));
   cronwalk::UnmetIn in;
   in.earliest = __ldg(a.earliest + ii);
@@ -262,15 +472,15 @@ __device__ __forceinline__ void unmet_one(const UnmetArgs& a, const ZoneTable& z
   in.active = a.active ? __ldg(a.active + ii) : 0;
   in.flags = a.flags ? __ldg(a.flags + ii) : 0;
   in.deadline = a.deadline ? __ldg(a.deadline + ii) : kZero;
-  const int32_t zone = a.zone_id ? __ldg(a.zone_id + ii) : 0;
+  const int32_t zone = (kMode != kUnmetUtc && a.zone_id) ? __ldg(a.zone_id + ii) : 0;
 
   bool ok = live;
   if (ok) {
     const int64_t lo = in.earliest < in.now ? in.earliest : in.now;
     if (lo < kMinTime || in.now > kMaxTime || in.earliest > kMaxTime) { atomicOr(err, kErrRange); ok = false; }
-    if (ok && zone != 0) {
+    if (kMode != kUnmetUtc && ok && zone != 0) {
       if (zone < 0 || zone >= zt.nzones) { atomicOr(err, kErrZone); ok = false; }
-      else if (__ldg(zt.zstart + zone + 1) - __ldg(zt.zstart + zone) > 1 && in.now >= zt.horizon - kSixYears) {
+      else if (!s.every && __ldg(zt.zstart + zone + 1) - __ldg(zt.zstart + zone) > 1 && in.now >= zt.horizon - kSixYears) {
         atomicOr(err, kErrRange); ok = false;
       }
     }
@@ -279,10 +489,17 @@ __device__ __forceinline__ void unmet_one(const UnmetArgs& a, const ZoneTable& z
   st.o.last = kZero; st.o.next = kZero; st.o.missed = 0; st.o.status = cronwalk::kStOk; st.o.decision = 0;
   st.done = true;
   st.w.bind_utc();
-  if (ok) cronwalk::unmet_begin(zt, zone, in, st);
+  if (ok) {
+    if (s.every) st.o = cronwalk::unmet_decide_every((int64_t)s.second, in);  // "@every <dur>": closed form, no walk
+    else cronwalk::unmet_begin(zt, zone, in, st);
+  }
   // all 32 lanes go round together: a full-mask vote per iteration is the reconvergence point
   bool defer = false;
-  if (kMode == kUnmetEasy) {
+  if (kMode == kUnmetUtc) {
+    while (__any_sync(0xffffffffu, !st.done)) {
+      if (!st.done) cronwalk::unmet_step_utc(s, in, st);
+    }
+  } else if (kMode == kUnmetEasy) {
 #pragma unroll 1
     for (int round = 0; round < kUnmetEasyRounds; ++round) {
       if (!__any_sync(0xffffffffu, !st.done)) break;
@@ -313,18 +530,80 @@ __device__ __forceinline__ void unmet_one(const UnmetArgs& a, const ZoneTable& z
   }
 }
 
-// kOrdered: the launch walks the Crons in the order of an index list (zone_order_* kernels below) instead of input order
-template <int kMode, bool kOrdered = false>
-__global__ void __launch_bounds__(kUnmetThreads, kMode == kUnmetEasy ? B200CRON_UNMET_EASY_MINBLOCKS : 12)
-unmet_kernel(UnmetArgs a, ZoneTable zt, int* __restrict__ err, uint32_t* __restrict__ defer_idx,
-             uint32_t* __restrict__ defer_count, const uint32_t* __restrict__ order = nullptr) {
+// the whole job in one launch with the general state machine: only for batches beyond 2^32 Crons (the index lists of
+// the other kernels are 32-bit)
+__global__ void __launch_bounds__(kUnmetThreads, 12)
+unmet_single_kernel(UnmetArgs a, ZoneTable zt, int* __restrict__ err) {
   const size_t q = (size_t)blockIdx.x * kUnmetThreads + threadIdx.x;
-  const bool live = q < a.n;
-  const size_t i = kOrdered ? (live ? (size_t)__ldg(order + q) : 0) : q;
-  unmet_one<kMode>(a, zt, err, i, live, defer_idx, defer_count);
+  unmet_one<kUnmetSingle>(a, zt, err, q, q < a.n, nullptr, nullptr);
 }
 
-// the general state machine over the compact list the easy kernel left behind (grid-stride: the host does not know
+// Input-order tiles with class-pure warps (see above).  kZoned: the zoned class is also handled here (easy rounds);
+// otherwise only the UTC class is, and the zoned Crons are left to unmet_ordered_kernel.  A launch without zone ids
+// is all UTC: no classification, no defer list.
+constexpr int kUnmetTile = 512;  // Crons per CTA: ~8 warps' worth per class on a half-UTC workload
+template <bool kZoned>
+__global__ void __launch_bounds__(kUnmetThreads, B200CRON_UNMET_EASY_MINBLOCKS)
+unmet_tile_kernel(UnmetArgs a, ZoneTable zt, int* __restrict__ err, uint32_t* __restrict__ defer_idx,
+                  uint32_t* __restrict__ defer_count) {
+  const size_t base = (size_t)blockIdx.x * kUnmetTile;
+  const int cnt = (int)((a.n - base) < (size_t)kUnmetTile ? (a.n - base) : (size_t)kUnmetTile);
+  if (a.zone_id == nullptr) {
+    for (int q = threadIdx.x; q < ((cnt + 31) & ~31); q += kUnmetThreads)
+      unmet_one<kUnmetUtc>(a, zt, err, base + q, q < cnt, nullptr, nullptr);
+    return;
+  }
+  // deal the tile's Crons into the two classes: UTC indices packed from the front of s_idx, zoned ones from the back
+  __shared__ uint16_t s_idx[kUnmetTile];
+  __shared__ int s_n[2];
+  if (threadIdx.x < 2) s_n[threadIdx.x] = 0;
+  __syncthreads();
+  const unsigned lane = threadIdx.x & 31u;
+#pragma unroll
+  for (int it = 0; it < kUnmetTile / kUnmetThreads; ++it) {
+    const int q = it * kUnmetThreads + threadIdx.x;
+    const bool in = q < cnt;
+    const bool zoned = in && __ldg(a.zone_id + base + q) != 0;
+    const unsigned mz = __ballot_sync(0xffffffffu, zoned), mu = __ballot_sync(0xffffffffu, in && !zoned);
+    int bu = 0, bz = 0;
+    if (lane == 0) {
+      if (mu) bu = atomicAdd(&s_n[0], __popc(mu));
+      if (mz) bz = atomicAdd(&s_n[1], __popc(mz));
+    }
+    bu = __shfl_sync(0xffffffffu, bu, 0);
+    bz = __shfl_sync(0xffffffffu, bz, 0);
+    const unsigned below = (1u << lane) - 1u;
+    if (in && !zoned) s_idx[bu + __popc(mu & below)] = (uint16_t)q;
+    if (zoned) s_idx[kUnmetTile - 1 - (bz + __popc(mz & below))] = (uint16_t)q;
+  }
+  __syncthreads();
+  const int nu = s_n[0], nz = s_n[1];
+  for (int q = threadIdx.x; q < ((nu + 31) & ~31); q += kUnmetThreads) {
+    const bool live = q < nu;
+    unmet_one<kUnmetUtc>(a, zt, err, base + (live ? s_idx[q] : 0), live, nullptr, nullptr);
+  }
+  if (kZoned) {
+    for (int q = threadIdx.x; q < ((nz + 31) & ~31); q += kUnmetThreads) {
+      const bool live = q < nz;
+      unmet_one<kUnmetEasy>(a, zt, err, base + (live ? s_idx[kUnmetTile - 1 - q] : 0), live, defer_idx, defer_count);
+    }
+  }
+}
+
+// the easy rounds over the zone-ordered index list (count = its length, known only on the device)
+__global__ void __launch_bounds__(kUnmetThreads, B200CRON_UNMET_EASY_MINBLOCKS)
+unmet_ordered_kernel(UnmetArgs a, ZoneTable zt, int* __restrict__ err, uint32_t* __restrict__ defer_idx,
+                     uint32_t* __restrict__ defer_count, const uint32_t* __restrict__ order,
+                     const uint32_t* __restrict__ order_count) {
+  const uint32_t cnt = __ldg(order_count);
+  const size_t q0 = (size_t)blockIdx.x * kUnmetThreads + (threadIdx.x & ~31u);
+  if (q0 >= cnt) return;  // warp-uniform
+  const size_t q = q0 + (threadIdx.x & 31u);
+  const bool live = q < cnt;
+  unmet_one<kUnmetEasy>(a, zt, err, live ? (size_t)__ldg(order + q) : 0, live, defer_idx, defer_count);
+}
+
+// the general state machine over the compact list the easy rounds left behind (grid-stride: the host does not know
 // the list's length when it launches)
 __global__ void __launch_bounds__(kUnmetThreads, B200CRON_UNMET_HARD_MINBLOCKS)
 unmet_hard_kernel(UnmetArgs a, ZoneTable zt, int* __restrict__ err, const uint32_t* __restrict__ defer_idx,
@@ -338,13 +617,9 @@ unmet_hard_kernel(UnmetArgs a, ZoneTable zt, int* __restrict__ err, const uint32
 }
 
 // -------------------------------------------------------------------------------------------------------------
-// Zone order (opt-in, B200CRON_UNMET_ZONE_ORDER=1; written at the end of round 1 and NOT yet run on a GPU -- see
-// DESIGN.md section 8).  The easy kernel spends its time in zone-dependent code that 4-5 of a warp's 32 lanes execute
-// together: half of the lanes are UTC and the zoned ones sit in different zones, hence in different periods.  A
-// counting sort of the Cron indices by zone id (histogram, scan, scatter; one pass over zone_id each) lets the easy
-// kernel walk zone-pure warps through an index list; inputs are then gathered and outputs scattered 8 bytes at a
-// time, which is cheap next to the divergence it removes.  Ids outside [0, nzones) are binned with UTC; unmet_one
-// reports them as before.
+// Zone order: a counting sort of the ZONED Crons' indices by zone id (histogram, scan, scatter; one pass over zone_id
+// each).  Crons evaluated in UTC (zone id 0) are left out -- the tile kernel handles them in place; ids outside
+// [0, nzones) are binned with zone 1 and reported by unmet_one as before.  cursor[nzones] receives the list's length.
 // -------------------------------------------------------------------------------------------------------------
 constexpr int kZoneOrderThreads = 256;
 constexpr int kZoneOrderItems = 16;  // Crons per thread: a CTA bins 4096 consecutive Crons
@@ -352,7 +627,7 @@ constexpr int kZoneOrderTile = kZoneOrderThreads * kZoneOrderItems;
 
 __device__ __forceinline__ uint32_t zone_bin(const int32_t* __restrict__ zone_id, size_t i, int32_t nzones) {
   const int32_t z = __ldg(zone_id + i);
-  return (z < 0 || z >= nzones) ? 0u : (uint32_t)z;
+  return (z < 0 || z >= nzones) ? 1u : (uint32_t)z;
 }
 
 // the CTA's histogram of its tile in shared memory (bins [0, nzones)); all threads call it
@@ -364,7 +639,10 @@ __device__ __forceinline__ void zone_tile_hist(const int32_t* __restrict__ zone_
 #pragma unroll 4
   for (int it = 0; it < kZoneOrderItems; ++it) {
     const size_t i = base + (size_t)it * kZoneOrderThreads + threadIdx.x;
-    if (i < n) atomicAdd(&sh[zone_bin(zone_id, i, nzones)], 1u);
+    if (i < n) {
+      const uint32_t b = zone_bin(zone_id, i, nzones);
+      if (b) atomicAdd(&sh[b], 1u);
+    }
   }
   __syncthreads();
 }
@@ -377,7 +655,8 @@ zone_order_hist_kernel(const int32_t* __restrict__ zone_id, size_t n, int32_t nz
     if (zo_sh[b]) atomicAdd(hist + b, zo_sh[b]);
 }
 
-// exclusive prefix sum of the histogram into `cursor` (one CTA; a thread owns a contiguous run of bins)
+// exclusive prefix sum of the histogram into `cursor` (one CTA; a thread owns a contiguous run of bins);
+// cursor[nzones] = total
 __global__ void __launch_bounds__(kZoneOrderThreads)
 zone_order_scan_kernel(const uint32_t* __restrict__ hist, int32_t nzones, uint32_t* __restrict__ cursor) {
   __shared__ uint32_t part[kZoneOrderThreads];
@@ -390,6 +669,7 @@ zone_order_scan_kernel(const uint32_t* __restrict__ hist, int32_t nzones, uint32
   if (threadIdx.x == 0) {
     uint32_t run = 0;
     for (int t = 0; t < kZoneOrderThreads; ++t) { const uint32_t v = part[t]; part[t] = run; run += v; }
+    cursor[nzones] = run;
   }
   __syncthreads();
   uint32_t run = part[threadIdx.x];
@@ -415,7 +695,7 @@ zone_order_scatter_kernel(const int32_t* __restrict__ zone_id, size_t n, int32_t
     const size_t i = base + (size_t)it * kZoneOrderThreads + threadIdx.x;
     if (i < n) {
       const uint32_t b = zone_bin(zone_id, i, nzones);
-      order[sh_base[b] + atomicAdd(&zo_sh[b], 1u)] = (uint32_t)i;
+      if (b) order[sh_base[b] + atomicAdd(&zo_sh[b], 1u)] = (uint32_t)i;
     }
   }
 }
@@ -621,11 +901,11 @@ unmet_list_emit_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const 
   if (i >= n) return;
   const uint64_t a = __ldg(list_off + i), b = __ldg(list_off + i + 1);
   if (b == a) return;
-  const Spec s = cronwalk::make_spec(__ldg(m.p[0] + i), __ldg(m.p[1] + i), __ldg(m.p[2] + i), __ldg(m.p[3] + i),
-                                     __ldg(m.p[4] + i), __ldg(m.p[5] + i));
+  const Spec s = cronwalk::make_spec(m.p[0] ? __ldg(m.p[0] + i) : 1ULL, __ldg(m.p[1] + i), __ldg(m.p[2] + i),
+                                     __ldg(m.p[3] + i), __ldg(m.p[4] + i), __ldg(m.p[5] + i));
   const int32_t zone = zone_id ? __ldg(zone_id + i) : 0;
   Walk w;
-  if (zone == 0) w.bind_utc(); else w.bind_zone(zt, zone);  // ids and ranges were validated by unmet_kernel
+  if (zone == 0) w.bind_utc(); else w.bind_zone(zt, zone);  // ids and ranges were validated by the unmet kernels
   int64_t t = __ldg(earliest + i);
   bool resident = false;
   for (uint64_t j = a; j < b; ++j) {

@@ -286,6 +286,8 @@ int parse(sv spec, bool seconds, b200cron_spec* out, int* kind, int64_t* every, 
       if (ns < 1000000000LL) ns = 1000000000LL;  // constantdelay.go Every(): at least one second, whole seconds
       if (kind) *kind = B200CRON_KIND_EVERY;
       if (every) *every = ns / 1000000000LL;
+      // the batch encoding of a ConstantDelaySchedule (include/b200cron.h): ready to drop into the six planes
+      *out = b200cron_spec{0, 0, 0, (uint64_t)(ns / 1000000000LL), B200CRON_EVERY_TAG, 0};
     } else {
       fail("unrecognized descriptor: %.*s", (int)spec.size(), spec.data());
     }

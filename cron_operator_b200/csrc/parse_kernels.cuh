@@ -6,7 +6,8 @@
 // which is checked against the oracle): optional TZ=/CRON_TZ= prefix, @descriptors, exactly 5 (or 6) whitespace
 // separated fields, comma lists of lo[-hi][/step] terms, `*`/`?`, names for month and day-of-week.
 // Zone names cannot be resolved on the device: the span of the name inside the spec is returned and the host maps
-// it to a zone id.  "@every <duration>" is flagged (status 2) and left to the host.
+// it to a zone id.  "@every <duration>" with plain h/m/s terms is parsed here; other durations are flagged (status 2)
+// and left to the host.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -170,7 +171,30 @@ parse_batch_kernel(const char* __restrict__ text, const uint64_t* __restrict__ t
       else if (equals(s, "@weekly", 7)) { m[2] = 1; m[3] = all_dom; m[4] = all_month; m[5] = 1; st = kParseOk; }
       else if (equals(s, "@daily", 6) || equals(s, "@midnight", 9)) { m[2] = 1; m[3] = all_dom; m[4] = all_month; m[5] = all_dow; st = kParseOk; }
       else if (equals(s, "@hourly", 7)) { m[2] = all_hour; m[3] = all_dom; m[4] = all_month; m[5] = all_dow; st = kParseOk; }
-      else if (starts_with(s, "@every ", 7)) { m[0] = 0; m[1] = 0; st = kParseEvery; }
+      else if (starts_with(s, "@every ", 7)) {
+        // time.ParseDuration restricted to what needs no care: one or more <digits><h|m|s> terms, at most 9 digits
+        // each (no overflow anywhere near Go's 2^63 ns).  Anything else -- sign, fraction, "ms"/"us"/"ns", a bare "0",
+        // an unknown unit -- goes to the host parser (status 2), which is ParseDuration to the letter.
+        m[0] = 0; m[1] = 0; st = kParseEvery;
+        uint64_t total = 0;
+        int k = 7;
+        bool simple = k < s.n;
+        while (simple && k < s.n) {
+          uint64_t v = 0;
+          int digits = 0;
+          while (k < s.n && ch(s, k) >= '0' && ch(s, k) <= '9' && digits < 10) { v = v * 10 + (uint64_t)(ch(s, k) - '0'); ++k; ++digits; }
+          if (digits == 0 || digits > 9 || k >= s.n) { simple = false; break; }
+          const char u = ch(s, k++);
+          const bool unit_ends = k >= s.n || (ch(s, k) >= '0' && ch(s, k) <= '9');  // the unit is this one letter
+          if (!unit_ends || !(u == 'h' || u == 'm' || u == 's')) { simple = false; break; }
+          total += v * (u == 'h' ? 3600ULL : u == 'm' ? 60ULL : 1ULL);
+        }
+        if (simple) {  // constantdelay.go Every(): at least one second
+          m[3] = total < 1 ? 1 : total;
+          m[4] = 1ULL << 62;  // B200CRON_EVERY_TAG
+          st = kParseOk;
+        }
+      }
       else { m[0] = 0; m[1] = 0; }
       break;
     }

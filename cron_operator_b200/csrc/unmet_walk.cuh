@@ -86,8 +86,12 @@ CW_HD int32_t last_tod_le(const Spec& s, int32_t sod) {
 //      wrap; while all those midnights are natural in this period the chain visits exactly the matching days, and
 //      each such day's fires are enumerated by (1).  The 5-year limit can only bite between two matching days: the
 //      fast-forward stops before any day whose year exceeds (last fire year + 5) and lets the literal call decide.
+// kUtcOnly: the walk is bound to UTC (one endless period, offset 0, everything natural): the zone logic compiles away.
+template <bool kUtcOnly = false>
 CW_HD void chain_fast_forward(const Spec& s, Walk& w, int64_t limit, uint32_t* missed) {
-  const bool edge59 = ((s.second >> 59) & 1ULL) && ((s.minute >> 59) & 1ULL);
+  // A Date() call inside a day can only be the hour reset, taken when the call starts on an exact hour start whose
+  // hour does not match: the spec must be able to fire at :59:59 AND exclude some hour.
+  const bool edge59 = !kUtcOnly && ((s.second >> 59) & 1ULL) && ((s.minute >> 59) & 1ULL) && (s.hour != 0xFFFFFFu);
   // A fire produced while a loop stepped across a transition can sit on fields upstream never re-checked (e.g. the
   // hour loop going 23h -> 01h over a midnight gap lands on a day that does not match).  The next call re-checks
   // them from scratch, so nothing may be assumed about such a fire: only fast-forward from a fully matching one.
@@ -98,8 +102,16 @@ CW_HD void chain_fast_forward(const Spec& s, Walk& w, int64_t limit, uint32_t* m
   const int64_t day_end = w.t + (86400 - w.sod);  // absolute instant of the next local midnight at this offset
   {
     int64_t lim_abs = limit < day_end - 1 ? limit : day_end - 1;
-    if (w.pe - 1 < lim_abs) lim_abs = w.pe - 1;
-    if (edge59 && !(w.natural(w.t + w.off) && w.natural(lim_abs + w.off))) return;
+    if (!kUtcOnly && w.pe - 1 < lim_abs) lim_abs = w.pe - 1;
+    bool hour_only = false;
+    if (edge59 && !(w.natural(w.t + w.off) && w.natural(lim_abs + w.off))) {
+      // Some hour start of the stretch may not resolve naturally.  No chained call starts on an hour start before the
+      // current local hour is over, so the rest of THIS hour is still a plain enumeration; the literal call that
+      // follows crosses the hour boundary the way upstream does (one literal call per hour instead of one per fire).
+      const int64_t hour_end = w.t + (3599 - w.sod % 3600);
+      if (hour_end < lim_abs) lim_abs = hour_end;
+      hour_only = true;
+    }
     const int32_t lim_sod = w.sod + (int32_t)(lim_abs - w.t);
     const int32_t last = last_tod_le(s, lim_sod);
     if (last > w.sod) {
@@ -107,25 +119,36 @@ CW_HD void chain_fast_forward(const Spec& s, Walk& w, int64_t limit, uint32_t* m
       w.t += last - w.sod;
       w.sod = last;
     }
+    if (hour_only) return;
   }
-  if (limit < day_end || day_end >= w.pe) return;
+  if (limit < day_end || (!kUtcOnly && day_end >= w.pe)) return;
 
   // ---- (2) whole following days whose midnights are natural in this period ----
   const int64_t kFar = (int64_t)1 << 46;  // ~2.2 million years: outside every supported input
-  const int64_t xmax = w.pe == kOmega ? kFar : w.pe - 1 + (w.off < 0 ? w.off : 0);
-  const int64_t xmin = w.ps == kAlpha ? -kFar : w.ps + (w.off > 0 ? w.off : 0);
-  int64_t dhi64 = xmax / 86400; if (xmax % 86400 < 0) --dhi64;   // floor
-  int64_t dlo64 = xmin / 86400; if (xmin % 86400 > 0) ++dlo64;   // ceil
-  const int32_t dhi = (int32_t)dhi64, dlo = (int32_t)dlo64;      // days d with natural(d * 86400): dlo <= d <= dhi
+  int32_t dhi = INT32_MAX / 2, dlo = INT32_MIN / 2;              // days d with natural(d * 86400): dlo <= d <= dhi
+  if (!kUtcOnly) {
+    const int64_t xmax = w.pe == kOmega ? kFar : w.pe - 1 + (w.off < 0 ? w.off : 0);
+    const int64_t xmin = w.ps == kAlpha ? -kFar : w.ps + (w.off > 0 ? w.off : 0);
+    int64_t dhi64 = xmax / 86400; if (xmax % 86400 < 0) --dhi64;   // floor
+    int64_t dlo64 = xmin / 86400; if (xmin % 86400 > 0) ++dlo64;   // ceil
+    dhi = (int32_t)dhi64; dlo = (int32_t)dlo64;
+  }
   int32_t cur = w.dn + 1;
   if (cur < dlo || cur > dhi) return;
 
-  const bool lim_inside = limit < w.pe;
+  const bool lim_inside = kUtcOnly || limit < w.pe;
   int32_t Ld = 0, Lsod = 0;
   if (lim_inside) {
-    const int64_t L = limit + w.off;
-    int64_t q = L / 86400; if (L % 86400 < 0) --q;
-    Ld = (int32_t)q; Lsod = (int32_t)(L - q * 86400);
+    const int64_t L = limit + (kUtcOnly ? 0 : w.off);
+    if (kUtcOnly) {  // |L| < 2^38 inside the supported range: floor-divide by 86400 = 128 * 675 in 32 bits
+      const int32_t hi = (int32_t)(L >> 7);
+      int32_t q = hi / 675, r = hi - q * 675;
+      if (r < 0) { r += 675; q -= 1; }
+      Ld = q; Lsod = r * 128 + (int32_t)(L & 127);
+    } else {
+      int64_t q = L / 86400; if (L % 86400 < 0) --q;
+      Ld = (int32_t)q; Lsod = (int32_t)(L - q * 86400);
+    }
   }
   int32_t full_last = dhi - 1;  // last day whose closing midnight is still natural
   if (lim_inside && Ld - 1 < full_last) full_last = Ld - 1;
@@ -166,10 +189,9 @@ CW_HD void chain_fast_forward(const Spec& s, Walk& w, int64_t limit, uint32_t* m
   *missed = sat_add(*missed, total);
   w.dn = last_dn;
   w.sod = last_sod;
-  w.t = (int64_t)last_dn * 86400 + last_sod - w.off;
+  w.t = (int64_t)last_dn * 86400 + last_sod - (kUtcOnly ? 0 : w.off);
   civil_from_days(last_dn, w.Y, w.M, w.D);
   w.today_ok = true;  // last_dn came out of the month's day mask
-  CW_DAY_PLAIN(w.day_plain = false;)
   w.dm_ok = false;
 }
 
@@ -203,17 +225,21 @@ CW_HD void unmet_finish(const UnmetIn& in, UnmetState& st) {
   else st.o.decision = kDecCreate;
 }
 
+// Reconcile's gates (:163-180); returns the gate's decision code, or 0 when the Cron goes on to getNextSchedule
+CW_HD uint8_t unmet_gate(const UnmetIn& in) {
+  if (in.flags & kFlagDeleted) return kDecGateDeleted;
+  if (in.flags & kFlagSuspend) return kDecGateSuspended;
+  // now.After(deadline): now carries nanoseconds, the deadline is a whole second
+  if (in.deadline != kZero && (in.now > in.deadline || (in.now == in.deadline && in.now_nsec > 0))) return kDecGateDeadline;
+  return 0;
+}
+
 CW_HD void unmet_begin(const ZoneTable& zt, int32_t zone, const UnmetIn& in, UnmetState& st) {
   st.o.last = kZero; st.o.next = kZero; st.o.missed = 0; st.o.status = kStOk; st.o.decision = 0;
   st.done = true;
   st.w.bind_utc();
-  if (in.flags & kFlagDeleted) { st.o.decision = kDecGateDeleted; return; }
-  if (in.flags & kFlagSuspend) { st.o.decision = kDecGateSuspended; return; }
-  // now.After(deadline): now carries nanoseconds, the deadline is a whole second
-  if (in.deadline != kZero && (in.now > in.deadline || (in.now == in.deadline && in.now_nsec > 0))) {
-    st.o.decision = kDecGateDeadline;
-    return;
-  }
+  st.o.decision = unmet_gate(in);
+  if (st.o.decision) return;
   if (zone != 0) st.w.bind_zone(zt, zone);
   st.after_now = in.earliest > in.now;  // :404-406
   st.final_phase = st.after_now;
@@ -285,7 +311,69 @@ CW_HD void unmet_step_easy(const Spec& s, const UnmetIn& in, UnmetState& st, boo
   st.resident = true;
 }
 
+// getNextSchedule + gates + decision for a ConstantDelaySchedule ("@every <dur>", constantdelay.go), which the
+// reference reaches through the same cron.Schedule interface (cron_controller.go:392,405,409,436).  Next(t) = t + delay
+// on whole seconds, so the loop at :409 visits earliest + delay, earliest + 2 delay, ... <= now: a division.
+CW_HD UnmetOut unmet_decide_every(int64_t delay, const UnmetIn& in) {
+  UnmetOut o;
+  o.last = kZero; o.next = kZero; o.missed = 0; o.status = kStOk;
+  o.decision = unmet_gate(in);
+  if (o.decision) return o;
+  o.next = in.now + delay;  // :405 / :436
+  if (in.earliest > in.now) {
+    o.status = kStEarliestAfterNow;
+    o.decision = kDecRequeueOnly;
+    return o;
+  }
+  const uint64_t k = (uint64_t)(in.now - in.earliest) / (uint64_t)delay;
+  o.missed = k > 0xffffffffULL ? 0xffffffffu : (uint32_t)k;
+  if (k) o.last = in.earliest + (int64_t)(k * (uint64_t)delay);
+  if (o.last == kZero) o.decision = kDecRequeueOnly;
+  else if (in.policy == kPolicyForbid && in.active > 0) o.decision = kDecSkipForbid;
+  else if (in.policy == kPolicyReplace) o.decision = kDecReplaceCreate;
+  else o.decision = kDecCreate;
+  return o;
+}
+
+// unmet_step for a Cron evaluated in UTC (zone id 0, or a launch without zone ids).  One endless period, every Date()
+// natural: the closed form always answers, chained calls never step backwards, and the call at :436 is redundant --
+// when the chain ends with cur <= now < t = Next(cur), Next(now) is that same t: in UTC Next(x) is the smallest matching
+// instant after x inside x's five-year window, no instant of (cur, t) matches, and t lies inside now's window because
+// it lies inside cur's (cur.Year() <= now.Year()).  So a Cron costs one Next() plus, when something was missed, one
+// fast-forward and one more Next().
+CW_HD void unmet_step_utc(const Spec& s, const UnmetIn& in, UnmetState& st) {
+  const int64_t t = next_from_t<false, true>(s, st.w, st.arg, st.resident);
+  if (st.final_phase) {  // earliest.After(now): Next(now) is the whole answer (:404-406)
+    st.o.next = t;
+    unmet_finish(in, st);
+    return;
+  }
+  if (t == kZero) {  // :410-412
+    st.o.last = kZero; st.o.missed = 0; st.o.status = kStUnschedulable; st.o.decision = kDecErrUnschedulable;
+    st.done = true;
+    return;
+  }
+  if (t > in.now) {
+    st.o.next = t;
+    unmet_finish(in, st);
+    return;
+  }
+  st.o.missed = sat_add(st.o.missed, 1);
+  chain_fast_forward<true>(s, st.w, in.now, &st.o.missed);
+  st.o.last = st.w.t;
+  st.arg = st.w.t;
+  st.resident = true;
+}
+
+CW_HD UnmetOut unmet_decide_utc(const Spec& s, const ZoneTable& zt, const UnmetIn& in) {
+  UnmetState st;
+  unmet_begin(zt, 0, in, st);
+  while (!st.done) unmet_step_utc(s, in, st);
+  return st.o;
+}
+
 CW_HD UnmetOut unmet_decide(const Spec& s, const ZoneTable& zt, int32_t zone, const UnmetIn& in) {
+  if (s.every) return unmet_decide_every((int64_t)s.second, in);
   UnmetState st;
   unmet_begin(zt, zone, in, st);
   while (!st.done) unmet_step(s, in, st);

@@ -427,6 +427,24 @@ bool build_zone_table(const std::string& zoneinfo_dir, int horizon_year, HostZon
     }
   }
   out->zstart.push_back((int32_t)out->when.size());
+  // year index (see zone_table.h); kYearBase / kYearStep are shared with the walk (cron_walk.cuh)
+  const int64_t kYearBase = -2208988800LL, kYearStep = 31536000LL;  // 1900-01-01T00:00:00Z, 365 days
+  const int32_t nb = (int32_t)((out->horizon - kYearBase + kYearStep - 1) / kYearStep);
+  out->ystride = nb + 1;
+  out->yidx.assign(out->names.size() * (size_t)out->ystride, 0);
+  for (size_t z = 0; z < out->names.size(); ++z) {
+    const int32_t a = out->zstart[z], zn = out->zstart[z + 1] - a;
+    int32_t i = 0;
+    for (int32_t b = 0; b <= nb; ++b) {
+      const int64_t t = kYearBase + (int64_t)b * kYearStep;
+      while (i + 1 < zn && out->when[a + i + 1] <= t) ++i;
+      out->yidx[z * (size_t)out->ystride + b] = (uint16_t)i;
+    }
+    if (zn > 65535) {
+      if (err) *err = "zone " + out->names[z] + " has too many periods for the year index";
+      return false;
+    }
+  }
   if (out->names.size() <= 1) {
     if (err) *err = "no TZif files found under " + zoneinfo_dir;
     return false;

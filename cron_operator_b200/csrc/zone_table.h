@@ -20,6 +20,12 @@ struct HostZoneTable {
   // fpre[i] (zone-relative prefix): number of transitions among this zone's entries 1..i whose gap or overlap
   // contains a local midnight -- the only transitions at which Date(y, m, d, 0, 0, 0) is not "natural"
   std::vector<int32_t> fpre;
+  // Year index: row z holds, for every 365-day bucket b since 1900-01-01 (kYearBase, kYearStep), the index (relative
+  // to the zone) of the period in force at the bucket's start.  A lookup reads two neighbouring entries and is left
+  // with the two or three periods of that bucket instead of a binary search over the whole zone (up to ~700 periods
+  // with footer rules expanded to 2200) -- on the device each step of that search is a dependent L2 access.
+  std::vector<uint16_t> yidx;      // names.size() rows of ystride entries
+  int32_t ystride = 0;             // buckets per row + 1
   int64_t horizon = 0;             // unix second up to which footer rules were expanded
   int horizon_year = 0;
 

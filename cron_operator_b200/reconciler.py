@@ -55,16 +55,6 @@ class ReconcileResult:
     history_keep: list = field(default_factory=list)    # the rest, in history order (:324-344)
 
 
-def _every_unmet(delay: int, earliest: int, now: int):
-    """getNextSchedule for ConstantDelaySchedule (robfig constantdelay.go: Next(t) = t + delay on whole seconds):
-    the chain earliest + k * delay <= now, then Next(now)"""
-    if earliest > now:
-        return api.ZERO, now + delay, 0
-    missed = (now - earliest) // delay
-    last = earliest + missed * delay if missed > 0 else api.ZERO
-    return last, now + delay, missed
-
-
 class BatchReconciler:
     def __init__(self, engine):
         self.engine = engine
@@ -106,10 +96,7 @@ class BatchReconciler:
                     res[i].error = f'unparsable cron "{c.schedule}": {s}'   # :394
                     res[i].decision = api.DEC_ERR_UNSCHEDULABLE
                 continue
-            if s.Every:
-                self._fan_out(res[i], c, now, *self._every(c, s.Every, now, now_nsec))
-                continue
-            batch.append(i)
+            batch.append(i)  # either kind of schedule: "@every" rides in the same batch (api.EVERY_TAG encoding)
             specs.append(s)
         if batch:
             cs = [crons[i] for i in batch]
@@ -134,22 +121,6 @@ class BatchReconciler:
         if c.deadline is not None and (now > c.deadline or (now == c.deadline and now_nsec > 0)):
             return api.DEC_GATE_DEADLINE      # :176-180 (now.After(deadline))
         return 0
-
-    def _every(self, c, delay, now, now_nsec):
-        gate = self._gate(c, now, now_nsec)
-        if gate:
-            return gate, api.ST_OK, api.ZERO, api.ZERO, 0
-        earliest = c.last_schedule_time if c.last_schedule_time is not None else c.creation_timestamp
-        last, nxt, missed = _every_unmet(delay, earliest, now)
-        if last == api.ZERO:
-            dec = api.DEC_REQUEUE_ONLY
-        elif api.POLICY[c.concurrency_policy] == api.POLICY["Forbid"] and c.active > 0:
-            dec = api.DEC_SKIP_FORBID
-        elif api.POLICY[c.concurrency_policy] == api.POLICY["Replace"]:
-            dec = api.DEC_REPLACE_CREATE
-        else:
-            dec = api.DEC_CREATE
-        return dec, api.ST_OK, last, nxt, min(missed, 0xFFFFFFFF)
 
     @staticmethod
     def _fan_out(r, c, now, decision, status, last, nxt, missed):

@@ -67,6 +67,14 @@ enum { B200CRON_FLAG_SUSPEND = 1, B200CRON_FLAG_DELETED = 2 };
 
 enum { B200CRON_KIND_SPEC = 0, B200CRON_KIND_EVERY = 1 };
 
+/* "@every <dur>" parses to robfig's ConstantDelaySchedule (constantdelay.go: Next(t) = t + Delay on whole seconds), which
+ * the reference reaches through the same cron.Schedule interface (cron_controller.go:392,405,409,436).  In a batch it
+ * travels in the same six planes: month == B200CRON_EVERY_TAG (a bit no parser sets) marks it and dom holds Delay in
+ * whole seconds (values below 1 are read as 1, as upstream's Every() clamps); the other four planes and the zone id
+ * are ignored.  b200cron_parse_* fill *out this way for KIND_EVERY, so next_n / unmet_since / unmet_list take mixed
+ * batches of both kinds. */
+#define B200CRON_EVERY_TAG (1ULL << 62)
+
 /* robfig/cron v3 spec.go SpecSchedule (the Location is carried separately as a zone name / id) */
 typedef struct b200cron_spec {
   uint64_t second, minute, hour, dom, month, dow;
@@ -92,8 +100,10 @@ int b200cron_parse_with_seconds(const char* spec, size_t len, b200cron_spec* out
 /* Batched form of b200cron_parse_standard / _with_seconds, run on the GPU (one thread per spec): the reference
  * re-parses every Cron's schedule on every reconcile (cron_controller.go:392).  Spec i is the bytes
  * text[text_off[i] .. text_off[i+1]).  Outputs per spec: the six masks (SoA planes, zero on error), status
- * (0 parsed, 1 not parsable -- call b200cron_parse_standard on it for upstream's message, 2 "@every <duration>":
- * a ConstantDelaySchedule, left to the host parser), and the span of the TZ=/CRON_TZ= location name inside the
+ * (0 parsed -- "@every" with a duration made of whole h/m/s terms, e.g. "@every 1h30m", comes back in the
+ * B200CRON_EVERY_TAG encoding; 1 not parsable -- call b200cron_parse_standard on it for upstream's message; 2 an
+ * "@every" whose duration has a sign, a fraction, a sub-second unit or more than 9 digits in a term: left to the
+ * host parser, which is time.ParseDuration to the letter), and the span of the TZ=/CRON_TZ= location name inside the
  * spec (tz_len 0 = no prefix; tz_off 0xFFFFFFFF = an empty name, i.e. UTC) for the caller to turn into a zone id
  * with b200cron_zone_id.  Same accept/reject decisions as the host parser.  The host-pointer form runs on the
  * context's first device; the _dev form takes device pointers.  Declared below the context functions' types. */
@@ -111,7 +121,9 @@ int b200cron_parse_batch_dev(b200cron_ctx* ctx, int dev_index, void* stream, con
  * (charts/cron-operator values.yaml:70-71 `useHostTimezone`).  horizon_year <= 0 selects the default (2200). */
 int b200cron_ctx_create(const int* devices, int ndev, const char* zoneinfo_dir, int horizon_year, b200cron_ctx** out);
 void b200cron_ctx_destroy(b200cron_ctx* ctx);
-const char* b200cron_last_error(const b200cron_ctx* ctx); /* ctx may be NULL: error of the last failed create */
+/* text of the calling thread's most recent failed call into this library (kept per thread: Reconcile runs on up to
+ * MaxConcurrentReconciles OS threads at once); ctx is unused and may be NULL */
+const char* b200cron_last_error(const b200cron_ctx* ctx);
 int b200cron_device_count(const b200cron_ctx* ctx);
 /* zone name -> id usable in zone_id[] (0 for "" and "UTC"); -1 when the name is unknown (LoadLocation error) */
 int b200cron_zone_id(const b200cron_ctx* ctx, const char* name);
@@ -130,7 +142,8 @@ void b200cron_host_free(void* p);
  * out[i*k + j] = the (j+1)-th fire time after from[i] (each the Next() of the previous one), or
  * B200CRON_ZERO_TIME from the first call that finds no fire time within upstream's 5-year search.
  * masks[p] points to plane p (n uint64 each).  masks[0] (seconds) may be NULL: every spec then fires at second 0, which
- * is what ParseStandard's 5-field grammar always produces -- 8 bytes per spec less to move.  When every buffer of the
+ * is what ParseStandard's 5-field grammar always produces -- 8 bytes per spec less to move (b200cron_unmet_since and
+ * the list calls accept the same).  When every buffer of the
  * host-pointer form is pinned host memory the kernels work on it in place over PCIe (no staging copies). */
 int b200cron_next_n(b200cron_ctx* ctx, const uint64_t* const masks[6], const int32_t* zone_id, const int64_t* from,
                     size_t n, int k, int64_t* out);
@@ -158,9 +171,10 @@ int b200cron_ctx_set_overlap(b200cron_ctx* ctx, int on);
  * Outputs per Cron: last (lastMissed, ZERO when none), next (Next(now)), missed (missedTimes, saturating at
  * UINT32_MAX; the caller emits TooManyMissedTimes when > 100, :431-434), status, decision.  RequeueAfter is
  * next - now (:192).  Gated Crons get ZERO times and missed 0.
- * Two kernels run per call: one answers the Crons whose chain the closed form can follow, the other runs the general
- * walk over the rest, which reach it through an index list in device memory owned by the context (4 bytes per Cron
- * of the largest batch seen, three lists per device, allocated when a larger batch first arrives; calls on different
+ * A call without zone ids is one kernel and uses no scratch.  With zone ids the Crons evaluated in UTC are answered in
+ * place, the zoned ones through an index list grouped by zone, and whatever the closed form cannot follow through a
+ * second list by the general walk: both lists live in device memory owned by the context (8 bytes per Cron of the
+ * largest batch seen, three such buffers per device, allocated when a larger batch first arrives; calls on different
  * streams are kept apart by events). */
 int b200cron_unmet_since(b200cron_ctx* ctx, const uint64_t* const masks[6], const int32_t* zone_id,
                          const int64_t* earliest, int64_t now, int32_t now_nsec, const uint8_t* policy,
@@ -178,7 +192,7 @@ int b200cron_unmet_since_dev(b200cron_ctx* ctx, int dev_index, void* stream, con
  *   list_off[i] (n+1 entries) = exclusive prefix sum of min(missed[i], cap) over Crons whose decision is
  *                                REQUEUE_ONLY / SKIP_FORBID / REPLACE_CREATE / CREATE (0 for gated or failed ones), and
  *   list[list_off[i] .. list_off[i+1]) = that Cron's first min(missed, cap) missed fire times in order.
- * list_cap is the capacity of `list` in entries; when it is too small the call returns B200CRON_ENOMEM after
+ * cap <= 1,048,576 (larger values are rejected with B200CRON_EINVAL).  list_cap is the capacity of `list` in entries; when it is too small the call returns B200CRON_ENOMEM after
  * filling list_off (list_off[n] is the capacity needed).  The host-pointer variant runs on the context's first
  * device. */
 int b200cron_unmet_list(b200cron_ctx* ctx, const uint64_t* const masks[6], const int32_t* zone_id,
@@ -208,6 +222,32 @@ int b200cron_unmet_list_emit_dev(b200cron_ctx* ctx, int dev_index, void* stream,
                                  const int32_t* zone_id, const int64_t* earliest, size_t n, const uint64_t* list_off,
                                  int64_t* list);
 
+/* ---- resident spec sets --------------------------------------------------------------------------------------- */
+
+/* Extension with no counterpart in the reference: a SpecSchedule is immutable once ParseStandard has built it
+ * (cron_controller.go:392) and a Cron's schedule changes only when its CR does (api/v1alpha1/cron_types.go:77), so a
+ * host that ticks the same Crons again and again need not ship 48 bytes of masks per Cron every time.  A spec set
+ * keeps the six mask planes (masks[0] may be NULL: second 0) and the zone ids (NULL: all UTC) resident in device
+ * memory, sharded contiguously over the context's devices like the host-pointer calls; the _set calls then move only
+ * the per-tick arrays (8 bytes in and 8k bytes out per spec for next_n_set).  n is fixed at creation;
+ * b200cron_specset_update overwrites specs [first, first + count) (masks[p] / zone_id point at the first replaced
+ * spec; give exactly the planes the set was created with) and returns when the new values are in place.  A set
+ * belongs to the context that created it and must be destroyed before it.  Host buffers of the _set calls follow the
+ * same rule as everywhere: all pinned -> used in place over PCIe, otherwise staged copies. */
+typedef struct b200cron_specset b200cron_specset;
+int b200cron_specset_create(b200cron_ctx* ctx, const uint64_t* const masks[6], const int32_t* zone_id, size_t n,
+                            b200cron_specset** out);
+int b200cron_specset_update(b200cron_specset* set, size_t first, size_t count, const uint64_t* const masks[6],
+                            const int32_t* zone_id);
+void b200cron_specset_destroy(b200cron_specset* set);
+size_t b200cron_specset_size(const b200cron_specset* set);
+/* b200cron_next_n / b200cron_unmet_since over the set's specs, in the set's order (same outputs, same errors) */
+int b200cron_next_n_set(b200cron_ctx* ctx, const b200cron_specset* set, const int64_t* from, int k, int64_t* out);
+int b200cron_unmet_since_set(b200cron_ctx* ctx, const b200cron_specset* set, const int64_t* earliest, int64_t now,
+                             int32_t now_nsec, const uint8_t* policy, const uint32_t* active, const uint8_t* flags,
+                             const int64_t* deadline, int64_t* last, int64_t* next, uint32_t* missed, uint8_t* status,
+                             uint8_t* decision);
+
 /* ---- finished-history ordering + pruning ---------------------------------------------------------------------- */
 
 /* Replaces sortByCreationTimestamp (cron_util.go:117-129) and the prune index rule of syncCronHistory
@@ -234,6 +274,13 @@ int b200cron_synth_times_dev(b200cron_ctx* ctx, int dev_index, void* stream, uin
                              int64_t lo, int64_t hi, uint64_t stream_id, int64_t* out);
 int b200cron_synth_zones_dev(b200cron_ctx* ctx, int dev_index, void* stream, uint64_t seed, uint64_t start, size_t n,
                              const int32_t* pool, size_t pool_len, double p_utc, int32_t* out);
+
+/* Test support: the Crons the most recent unmet_since launch on device dev_index could not answer with the closed form
+ * and handed to the general walk (indices relative to that launch's arrays; up to `cap` of them are copied to
+ * idx_host, *count receives how many there were).  Waits for `stream` first.  Lets a parity test aim its oracle
+ * samples at exactly the Crons that took the rare path. */
+int b200cron_debug_last_deferred(b200cron_ctx* ctx, int dev_index, void* stream, uint32_t* idx_host, size_t cap,
+                                 size_t* count);
 
 /* `_dev` calls only enqueue work: this waits for `stream` (NULL = the context's stream) on device dev_index and
  * reports what the kernels flagged since the last check (B200CRON_ERANGE for out-of-range times / zone ids). */

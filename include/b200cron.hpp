@@ -79,8 +79,7 @@ class Engine {
 
   // Schedule.Next(t) for one schedule (a batch of one: launch latency dominates -- use NextN for work)
   int64_t Next(const Schedule& s, int64_t t) {
-    if (s.every > 0) return t + s.every;  // constantdelay.go on whole seconds
-    return NextN({s}, {t}, 1)[0];
+    return NextN({s}, {t}, 1)[0];  // either kind: an "@every" schedule rides in the planes (B200CRON_EVERY_TAG)
   }
 
   // out[i*k + j] = the (j+1)-th fire time after from[i]
@@ -118,11 +117,6 @@ class Engine {
       s = ParseStandard(schedule);
     } catch (const Error& e) {
       throw Error(e.code, "unparsable cron \"" + schedule + "\": " + e.what());
-    }
-    if (s.every > 0) {
-      if (earliest > now) return {kZeroTime, now + s.every};
-      const int64_t missed = (now - earliest) / s.every;
-      return {missed > 0 ? earliest + missed * s.every : kZeroTime, now + s.every};
     }
     const Unmet u = UnmetSince({s}, {earliest}, now)[0];
     if (u.status == B200CRON_ST_UNSCHEDULABLE || u.status == B200CRON_ST_NONTERMINATING)

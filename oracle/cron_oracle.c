@@ -948,6 +948,7 @@ static int parse_impl(const char* spec, size_t len, int with_seconds, orc_spec* 
       if (ns < 1000000000LL) ns = 1000000000LL;
       *kind = ORC_KIND_EVERY;
       *every_sec = ns / 1000000000LL;
+      *out = (orc_spec){0, 0, 0, (uint64_t)*every_sec, ORC_EVERY_TAG, 0}; /* batch encoding, see cron_oracle.h */
       return 0;
     }
     pfail(&e, "unrecognized descriptor: %.*s", (int)len, spec);
@@ -999,6 +1000,20 @@ int orc_parse_with_seconds(const char* s, size_t len, orc_spec* out, int* kind, 
   return parse_impl(s, len, 1, out, kind, every_sec, tz, tzcap, err, errcap);
 }
 
+/* constantdelay.go: func (schedule ConstantDelaySchedule) Next(t time.Time) time.Time {
+ *   return t.Add(schedule.Delay - time.Duration(t.Nanosecond())*time.Nanosecond) }
+ * Times are whole seconds at this boundary, so the nanosecond term is zero.  Every() never builds a Delay below one
+ * second; a hand-built plane that says so is clamped the same way. */
+int64_t orc_sched_next(const orc_spec* s, const orc_loc* loc, int64_t t) {
+  if (s->month == ORC_EVERY_TAG) {
+    int64_t delay = (int64_t)s->dom;
+    if (delay < 1) delay = 1;
+    g_steps = 0;
+    return t + delay;
+  }
+  return orc_spec_next(s, loc, t);
+}
+
 /* ------------------------------------------------------------------------------------------------
  * internal/controller/cron_controller.go
  * ---------------------------------------------------------------------------------------------- */
@@ -1009,7 +1024,7 @@ int orc_get_next_schedule(const orc_spec* s, const orc_loc* loc, int64_t earlies
   *next = ORC_ZERO;
   *missed = 0;
   if (earliest > now) { /* :404-406 */
-    *next = orc_spec_next(s, loc, now);
+    *next = orc_sched_next(s, loc, now);
     return ORC_ST_EARLIEST_AFTER_NOW;
   }
   uint64_t missed_times = 0;
@@ -1022,19 +1037,19 @@ int orc_get_next_schedule(const orc_spec* s, const orc_loc* loc, int64_t earlies
    * loop is in a cycle exactly when it revisits a fire time: after each backward step the largest origin is kept and
    * a fire equal to it ends the call with ORC_ST_NONTERMINATING. */
   int64_t anchor = ORC_ZERO;
-  int64_t t = orc_spec_next(s, loc, earliest);
+  int64_t t = orc_sched_next(s, loc, earliest);
   while (t == ORC_ZERO || t <= now) {
     if (t == ORC_ZERO) return ORC_ST_UNSCHEDULABLE; /* :410-412 */
     last = t;
     missed_times++;
-    int64_t tn = orc_spec_next(s, loc, t);
+    int64_t tn = orc_sched_next(s, loc, t);
     if (tn != ORC_ZERO && tn <= t && t > anchor) anchor = t;
     if (anchor != ORC_ZERO && tn == anchor) return ORC_ST_NONTERMINATING;
     t = tn;
   }
   *last_missed = last;
   *missed = missed_times;
-  *next = orc_spec_next(s, loc, now); /* :436 */
+  *next = orc_sched_next(s, loc, now); /* :436 */
   return ORC_ST_OK;
 }
 
@@ -1138,7 +1153,7 @@ static void* worker(void* p) {
     if (j->which == 0) {
       int64_t t = j->from[i];
       for (int q = 0; q < j->k; q++) {
-        if (t != ORC_ZERO) t = orc_spec_next(&s, loc, t);
+        if (t != ORC_ZERO) t = orc_sched_next(&s, loc, t);
         j->out[i * (size_t)j->k + q] = t;
       }
     } else {
@@ -1214,7 +1229,7 @@ uint64_t orc_batch_unmet_list(const uint64_t* const masks[6], const int32_t* zon
       const orc_loc* loc = (zone_id && locs) ? locs[zone_id[i]] : NULL;
       int64_t t = earliest[i];
       for (uint32_t j = 0; j < c; j++) {
-        t = orc_spec_next(&s, loc, t);
+        t = orc_sched_next(&s, loc, t);
         if (run + j < list_cap) list[run + j] = t;
       }
     }

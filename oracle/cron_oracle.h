@@ -38,6 +38,11 @@ typedef struct {
 
 enum { ORC_KIND_SPEC = 0, ORC_KIND_EVERY = 1 };
 
+/* A ConstantDelaySchedule (constantdelay.go, what ParseStandard returns for "@every <dur>") travels through the
+ * batched entry points in the same six planes: month == ORC_EVERY_TAG (a bit no parser sets) marks it and dom holds
+ * Delay in whole seconds; the other four planes are ignored.  The parsers fill *out this way for @every. */
+#define ORC_EVERY_TAG (1ULL << 62)
+
 typedef struct orc_loc orc_loc; /* restatement of Go's time.Location */
 
 /* time.LoadLocation(name) reading TZif files below `zoneinfo_dir` (Go: zoneinfo_read.go). */
@@ -63,6 +68,9 @@ int orc_parse_with_seconds(const char* s, size_t len, orc_spec* out, int* kind, 
 int64_t orc_spec_next(const orc_spec* s, const orc_loc* loc, int64_t t);
 /* number of loop-body iterations the last orc_spec_next on this thread executed */
 int64_t orc_last_steps(void);
+/* Schedule.Next(t) for either kind: SpecSchedule (orc_spec_next) or ConstantDelaySchedule
+ * (constantdelay.go Next: t.Add(Delay - t.Nanosecond()); whole seconds here, Delay clamped to >= 1s as Every() does) */
+int64_t orc_sched_next(const orc_spec* s, const orc_loc* loc, int64_t t);
 
 /* getNextSchedule (cron_controller.go:389-437) on an already-parsed spec.
  * status: 0 ok, 1 "unschedulable cron" error, 2 earliest.After(now) early return, 3 upstream's loop would never

@@ -7,6 +7,9 @@ import torch
 sys.path.insert(0, ".")
 from cron_operator_b200 import api, synth  # noqa: E402
 
+import os  # noqa: E402
+
+api.lib(os.environ.get("B200CRON_LIB") or None)  # A/B: a tuning build from profiles/build_variants.sh
 which = sys.argv[1]
 n = int(sys.argv[2]) if len(sys.argv) > 2 else 2_000_000
 ctx = api.Context(devices=[0])
@@ -43,7 +46,7 @@ if which == "next1":
             ev1.record()
             ctx.sync_check(stream=st)
             best = min(best, ev0.elapsed_time(ev1) / K)
-        print("next1 overlap", ov, "us/step", best * 1e3, "roofline frac", 64e6 / (best * 1e-3) / 1e9 / 6555.5)
+        print("next1 overlap", ov, "us/step", best * 1e3, "roofline frac", 64e6 / (best * 1e-3) / 1e9 / 6536.7)
     ctx.close()
     sys.exit(0)
 if which == "unmet":

@@ -43,6 +43,8 @@ static ZoneTable view(void* t) {
   z.off = h->off.data();
   z.fpre = h->fpre.data();
   z.zstart = h->zstart.data();
+  z.yidx = h->yidx.data();
+  z.ystride = h->ystride;
   z.nzones = (int32_t)h->names.size();
   z.horizon = h->horizon;
   return z;
@@ -85,7 +87,9 @@ void shim_unmet(void* table, const uint64_t* const masks[6], const int32_t* zone
     in.active = active ? active[i] : 0;
     in.flags = flags ? flags[i] : 0;
     in.deadline = deadline ? deadline[i] : kZero;
-    UnmetOut o = unmet_decide(s, zt, zone_id ? zone_id[i] : 0, in);
+    // as the kernels do: Crons evaluated in UTC (no zone ids, or id 0) take the UTC machine, the rest the general one
+    const int32_t z = zone_id ? zone_id[i] : 0;
+    UnmetOut o = s.every ? unmet_decide_every((int64_t)s.second, in) : z == 0 ? unmet_decide_utc(s, zt, in) : unmet_decide(s, zt, z, in);
     last[i] = o.last; next[i] = o.next; missed[i] = o.missed; status[i] = o.status; decision[i] = o.decision;
   }
 }
@@ -114,6 +118,10 @@ void shim_unmet_two_phase(void* table, const uint64_t* const masks[6], const int
     unmet_begin(zt, z, in, st);
     bool defer = false;
     int r = 0;
+    if (s.every) {
+      st.o = unmet_decide_every((int64_t)s.second, in);
+      st.done = true;
+    }
     if (easy_rounds > 0) {
       while (!st.done) {
         if (r >= easy_rounds) { defer = true; break; }

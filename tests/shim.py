@@ -17,7 +17,7 @@ _TABLES = {}
 def lib():
     global _LIB
     if _LIB is None:
-        # B200CRON_SHIM_FLAGS: extra -D flags for the walk (e.g. -DB200CRON_WALK_DAY_PLAIN=1), built into its own .so
+        # B200CRON_SHIM_FLAGS: extra -D flags for the walk, built into its own .so (test-only tuning hook)
         extra = os.environ.get("B200CRON_SHIM_FLAGS", "").split()
         tag = "".join(c if c.isalnum() else "_" for c in "".join(extra))
         so = os.path.join(HERE, "host_shim", f"libwalk_host{tag}.so")

@@ -429,14 +429,14 @@ def test_device_parse_matches_host_parser(ctx):
                 want = api._parse(t, with_seconds)
             except api.ParseError:
                 want = None
-            if status[i] == 2:  # "@every ..." is always handed to the host parser, which validates the duration
+            if status[i] == 2:  # an "@every ..." the device hands to the host parser, which validates the duration
                 assert b"@every " in t and (want is None or want.Every), t
                 continue
             if want is None:
                 assert status[i] == 1, (t, status[i])
                 assert not masks[:, i].any()
-            elif want.Every:
-                assert status[i] == 2, t
+            elif want.Every:  # plain h/m/s durations are parsed on the device, into the EVERY_TAG encoding
+                assert status[i] == 0 and tuple(int(x) for x in masks[:, i]) == want.masks(), t
             else:
                 assert status[i] == 0, (t, status[i])
                 assert tuple(int(x) for x in masks[:, i]) == want.masks(), t
@@ -556,3 +556,185 @@ def test_unmet_kernel_pair_on_concurrent_streams(ctx, names):
         want = po.batch_unmet(masks, earliest, now, zone_id=zid, zone_names=names)
         got = {k: v.cpu().numpy().view(want[k].dtype) for k, v in o.items()}
         _cmp(got, want, len(earliest))
+
+
+def test_every_schedules_on_the_device(ctx, names):
+    """ConstantDelaySchedule ("@every <dur>", robfig constantdelay.go; reached by the reference at
+    cron_controller.go:392,405,409,436) as a schedule kind inside ordinary batches: next_n (k = 1 and chained),
+    unmet_since (pageable and pinned buffers), the unmet list and the device parser"""
+    from tests.test_unmet_host import every_batch
+    masks, is_every, delay, earliest, now = every_batch(50_001, seed=7)
+    n = masks.shape[1]
+    zid = np.where(np.arange(n) % 3 == 0, names.index("Europe/Berlin"), 0).astype(np.int32)
+    for k in (1, 4, 5):
+        got = ctx.next_n(masks, earliest, k, zid)
+        assert np.array_equal(got, po.batch_next_n(masks, earliest, k, zid, names)), k
+        assert np.array_equal(got[is_every], earliest[is_every, None] + delay[is_every, None] * np.arange(1, k + 1))
+    assert np.array_equal(ctx.next_n(masks, earliest, 1), po.batch_next_n(masks, earliest, 1))  # all-UTC kernel
+    rng = np.random.default_rng(1)
+    policy, active = rng.integers(0, 3, n).astype(np.uint8), rng.integers(0, 3, n).astype(np.uint32)
+    flags = (rng.random(n) < 0.05).astype(np.uint8)
+    for z in (zid, None):
+        got = ctx.unmet_since(masks, earliest, now, 0, policy, active, flags, None, z)
+        _cmp(got, po.batch_unmet(masks, earliest, now, 0, policy, active, flags, None, z, names if z is not None else None))
+    off, lst = ctx.unmet_list(masks, earliest, got["missed"], got["decision"], 100)
+    woff, wlst = po.batch_unmet_list(masks, earliest, got["missed"], got["decision"], 100)
+    assert np.array_equal(off, woff) and np.array_equal(lst, wlst)
+    # the reference's scalar shapes through the same path
+    s = api.ParseStandard("@every 1h30m")
+    assert ctx.Next(s, 1000) == 1000 + 5400
+    assert ctx.getNextSchedule("@every 90s", now - 200, now) == (now - 20, now + 90)
+    # device parser: plain h/m/s durations come back encoded, the rest goes to the host parser
+    texts = ["@every 90s", "@every 1h30m", "@every 0s", "@every 2h0m1s", "@every 1.5h", "@every 500ms", "@every -5s",
+             "@every 1h 30m", "@every 12345678901s", "@every 999999999h", "@every", "@every 5", "@every 5x", "@every 0"]
+    m, status, _ = ctx.parse_batch(texts)
+    for i, t in enumerate(texts):
+        try:
+            want = api.ParseStandard(t)
+        except api.ParseError:
+            want = None
+        if status[i] == 0:
+            assert want is not None and tuple(int(x) for x in m[:, i]) == want.masks(), t
+        else:
+            assert status[i] == 2 if t.startswith("@every ") else status[i] == 1, (t, status[i])
+    assert status[:4].tolist() == [0, 0, 0, 0] and int(m[3, 2]) == 1 and int(m[3, 3]) == 7201
+
+
+def test_unmet_null_seconds_plane_and_every_second_specs(ctx, names):
+    """masks[0] == NULL means second 0 for unmet_since too; and the chains of specs that fire every second are
+    fast-forwarded hour by hour next to a transition (they used to be walked one fire at a time)"""
+    n = 30_001
+    masks = synth.gen_specs(n, seed=17, dense_minutes=0.3)
+    zid = synth.gen_zone_ids(n, len(names), _dst_zones(ctx, names), seed=17)
+    now = ts(2026, 3, 29, 12)
+    earliest = now - synth.gen_times(n, 0, 3 * 86400, seed=17)
+    want = po.batch_unmet(masks, earliest, now, zone_id=zid, zone_names=names)
+    out = dict(last=np.empty(n, np.int64), next=np.empty(n, np.int64), missed=np.empty(n, np.uint32),
+               status=np.empty(n, np.uint8), decision=np.empty(n, np.uint8))
+    planes = api._planes(masks, five_field=True)[0]
+    ctx._check(api.lib().b200cron_unmet_since(ctx._h, planes, zid.ctypes.data, earliest.ctypes.data, now, 0, None, None,
+                                              None, None, n, out["last"].ctypes.data, out["next"].ctypes.data,
+                                              out["missed"].ctypes.data, out["status"].ctypes.data,
+                                              out["decision"].ctypes.data))
+    _cmp(out, want)
+    texts = ["* * 0-5,9,22-23 * * *", "*/7 * 1-3 * * *", "59 59 * * * *", "* 59 0,2,4,23 * * *", "* * * * * *",
+             "30-59 * 3-4 * * *", "* * 12 * * *"]
+    base = _masks_of(texts, with_seconds=True)
+    zs = [names.index(z) for z in ("Europe/Oslo", "Europe/Chisinau", "America/New_York", "Australia/Lord_Howe",
+                                   "Asia/Tehran", "America/Havana", "Pacific/Chatham", "UTC")]
+    S, Z = len(texts), len(zs)
+    m = np.ascontiguousarray(np.tile(base, (1, Z)))
+    z = np.repeat(np.array(zs, np.int32), S)
+    for back in (6 * 3600, 86400 + 1800, 3 * 86400):
+        e = np.full(S * Z, now - back)
+        got = ctx.unmet_since(m, e, now, zone_id=z)
+        _cmp(got, po.batch_unmet(m, e, now, zone_id=z, zone_names=names), back)
+
+
+def test_resident_spec_set(ctx, names):
+    """b200cron_specset_*: masks and zone ids stay in HBM, a tick moves only times in and results out; answers must be
+    those of the host-pointer calls (and so the oracle's), through pageable and pinned per-tick buffers, after an
+    update of a range, and for 5-field sets without a seconds plane"""
+    n = 300_001
+    masks = synth.gen_specs(n, seed=21, dense_minutes=0.2)
+    zid = synth.gen_zone_ids(n, len(names), _dst_zones(ctx, names), seed=21)
+    frm = synth.gen_times(n, ts(2024), ts(2034), seed=21)
+    P = api.PinnedArray
+    hf, ho1, ho4 = P(n, np.int64), P((n, 1), np.int64), P((n, 4), np.int64)
+    hf.array[:] = frm
+    for five, z in ((False, zid), (True, None)):
+        st = ctx.specset(masks, z, five_field=five)
+        try:
+            assert len(st) == n
+            want1 = po.batch_next_n(masks, frm, 1, z, names if z is not None else None)
+            want4 = po.batch_next_n(masks, frm, 4, z, names if z is not None else None)
+            assert np.array_equal(st.next_n(frm, 1), want1)                      # pageable: staged
+            assert np.array_equal(st.next_n(hf.array, 1, out=ho1.array), want1)  # pinned: in place
+            assert np.array_equal(st.next_n(hf.array, 4, out=ho4.array), want4)
+            assert np.array_equal(st.next_n(frm, 4), want4)
+            now = ts(2026, 3, 29, 12)
+            m = 60_000
+        finally:
+            st.close()
+    # unmet over a set, then an update of a range in the middle
+    m = 80_001
+    mm = np.ascontiguousarray(masks[:, :m])
+    now = ts(2026, 3, 29, 12)
+    earliest = now - synth.gen_times(m, 0, 2 * 86400, seed=22)
+    rng = np.random.default_rng(3)
+    policy, active = rng.integers(0, 3, m).astype(np.uint8), rng.integers(0, 3, m).astype(np.uint32)
+    st = ctx.specset(mm, zid[:m])
+    try:
+        want = ctx.unmet_since(mm, earliest, now, 0, policy, active, None, None, zid[:m])
+        _cmp(st.unmet_since(earliest, now, 0, policy, active), want, "pageable")
+        he, hp, ha = P(m, np.int64), P(m, np.uint8), P(m, np.uint32)
+        he.array[:] = earliest; hp.array[:] = policy; ha.array[:] = active
+        owners = dict(last=P(m, np.int64), next=P(m, np.int64), missed=P(m, np.uint32), status=P(m, np.uint8), decision=P(m, np.uint8))
+        out = {k: v.array for k, v in owners.items()}
+        _cmp(st.unmet_since(he.array, now, 0, hp.array, ha.array, out=out), want, "pinned")
+        lo, cnt = 12_345, 3_001
+        new_m = synth.gen_specs(cnt, seed=99)
+        new_z = np.zeros(cnt, np.int32)
+        st.update(lo, new_m, new_z)
+        mm2, z2 = mm.copy(), zid[:m].copy()
+        mm2[:, lo:lo + cnt] = new_m
+        z2[lo:lo + cnt] = 0
+        _cmp(st.unmet_since(earliest, now, 0, policy, active), po.batch_unmet(mm2, earliest, now, 0, policy, active, None, None, z2, names), "updated")
+        with pytest.raises(api.B200CronError):
+            st.update(m - 5, new_m, new_z)  # range outside the set
+    finally:
+        st.close()
+
+
+def _c4_inputs(n4, now):
+    """the C4 workload exactly as bench.py generates it (seed 41, dense minutes 0.5, 30-day backlog)"""
+    rng = np.random.default_rng(41)
+    pol = rng.integers(0, 3, n4).astype(np.uint8)
+    act = rng.choice([0, 1, 2], size=n4, p=[.6, .3, .1]).astype(np.uint32)
+    fl = (rng.random(n4) < 0.02).astype(np.uint8)
+    dl = np.where(rng.random(n4) < 0.01, now - 100, -2**63).astype(np.int64)
+    return pol, act, fl, dl
+
+
+def test_C4_full_size_sampled_parity(ctx, names):
+    """BASELINE config 4 at its full size and on the benched distribution (no thinning of the dense specs): 10M Crons
+    with a 30-day backlog, now inside a European DST day (getNextSchedule, cron_controller.go:389-437).  Oracle parity
+    on every 997th Cron plus a sample of the Crons the closed form gave up on (the general-walk path)."""
+    import torch
+    n4 = 10_000_000
+    now = ts(2026, 3, 29, 12)
+    st = torch.cuda.current_stream().cuda_stream
+    dst = _dst_zones(ctx, names)
+    pool = torch.from_numpy(synth.zone_pool(len(names), dst)).cuda()
+    dm = torch.empty((6, n4), dtype=torch.int64, device="cuda")
+    dz = torch.empty(n4, dtype=torch.int32, device="cuda")
+    de = torch.empty(n4, dtype=torch.int64, device="cuda")
+    ctx.synth_specs_dev(dm, n4, 41, 0, False, 0.5, stream=st)
+    ctx.synth_zones_dev(dz, n4, pool, 41, 0, stream=st)
+    ctx.synth_times_dev(de, n4, -86400, 86400, 41, 0, stream=st)
+    de += now - 30 * 86400
+    pol, act, fl, dl = _c4_inputs(n4, now)
+    t = lambda a: torch.from_numpy(a).cuda()  # noqa: E731
+    o = dict(last=torch.empty(n4, dtype=torch.int64, device="cuda"), next=torch.empty(n4, dtype=torch.int64, device="cuda"),
+             missed=torch.empty(n4, dtype=torch.int32, device="cuda"), status=torch.empty(n4, dtype=torch.uint8, device="cuda"),
+             decision=torch.empty(n4, dtype=torch.uint8, device="cuda"))
+    ctx.unmet_since_dev(dm, de, now, o, 0, t(pol), t(act), t(fl), t(dl), dz, stream=st)
+    ctx.sync_check(stream=st)
+    deferred, ndef = ctx.last_deferred(stream=st)
+    assert 0 < ndef < n4 // 10 and len(deferred) == ndef
+    idx = np.unique(np.concatenate([np.arange(0, n4, 997), np.sort(deferred)[::97].astype(np.int64)])).astype(np.uint64)
+    ms = synth.gen_specs(0, 41, dense_minutes=0.5, idx=idx)
+    zs = synth.gen_zone_ids(0, len(names), dst, 41, idx=idx)
+    es = now - 30 * 86400 + synth.gen_times(0, -86400, 86400, 41, idx=idx)
+    ii = idx.astype(np.int64)
+    want = po.batch_unmet(ms, es, now, 0, pol[ii], act[ii], fl[ii], dl[ii], zs, names)
+    gi = torch.from_numpy(ii).cuda()
+    got = {k: v[gi].cpu().numpy().view(want[k].dtype) for k, v in o.items()}
+    _cmp(got, want, "C4 sample")
+    assert want["missed"].max() >= 43_000      # the `* * * * *` chains were really walked by the oracle
+    # size-independent properties over all 10M: next > now unless failed/gated; last <= now; decision consistent
+    nxt, last, dec, miss = o["next"], o["last"], o["decision"], o["missed"].to(torch.int64)
+    live = dec >= api.DEC_REQUEUE_ONLY
+    assert bool(((nxt > now) | ~live).all()) and bool(((last <= now) | (last == po.ZERO)).all())
+    assert bool(((miss > 0) == ((last != po.ZERO) & live))[live].all())
+    assert bool(((dec == api.DEC_REQUEUE_ONLY) == (live & (last == po.ZERO)))[live].all())

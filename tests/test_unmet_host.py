@@ -203,3 +203,87 @@ def test_easy_hard_split_equals_general_machine(easy_rounds):
     zz = np.array([z], np.int32)
     got = shim.unmet_two_phase(m, np.array([1838162695]), 1839851648, easy_rounds, zone_id=zz)
     assert got["status"][0] == po.ST_NONTERMINATING and got["deferred"][0] == 1
+
+
+def test_every_second_specs_around_transitions_fast_forward_by_the_hour():
+    """specs that can fire at :59:59 and exclude some hour (the only ones whose chained calls can hit a Date() hour
+    reset): near a transition the fast-forward works hour by hour instead of giving up; same answers as the literal
+    chain, and the general machine needs few steps (it used to take one step per fire)"""
+    texts = ["* * 0-5,9,22-23 * * *", "*/7 * 1-3 * * *", "59 59 * * * *", "* 59 0,2,4,23 * * *", "* * * * * *",
+             "30-59 * 3-4 * * *", "* * 12 * * *"]
+    base = _masks_of(texts, with_seconds=True)
+    for name in ["Europe/Oslo", "Europe/Chisinau", "America/New_York", "Australia/Lord_Howe", "Asia/Tehran",
+                 "America/Havana", "Pacific/Chatham"]:
+        z = NAMES.index(name)
+        when = shim.zone_entries(z)[0]
+        for t in [int(w) for w in when if ts(2024) < w < ts(2028)][:4]:
+            for a, b in [(-6 * 3600, 5 * 3600), (-86400, 11 * 3600), (-2 * 86400, -1), (-100, 7200), (0, 3 * 3600)]:
+                S = len(texts)
+                zz = np.full(S, z, np.int32)
+                got = shim.unmet_two_phase(base, np.full(S, t + a), t + b, 0, zone_id=zz)
+                want = po.batch_unmet(base, np.full(S, t + a), t + b, zone_id=zz, zone_names=NAMES)
+                _cmp(got, want, (name, t, a, b))
+                ok = got["status"] == 0
+                assert got["rounds"][ok].max() < 120, (name, t, a, b, got["rounds"])
+
+
+def test_utc_machine_skips_the_final_call_exactly():
+    """unmet_step_utc answers Next(now) with the Next() that ended the chain; pin that against the literal restatement
+    where the two calls have different five-year windows (Feb 29 across 2100, year ends) and on random specs"""
+    texts = ["0 0 29 2 *", "0 0 31 12 *", "59 23 31 12 *", "0 0 1 1 *", "*/5 * * * *", "0 0 29 2 1", "0 12 30 4,6 *"]
+    base = _masks_of(texts)
+    S = len(texts)
+    for now in [ts(2099, 6, 1), ts(2100, 3, 1), ts(2101, 3, 1), ts(2104, 2, 29), ts(2096, 2, 29) - 1, ts(2096, 2, 29),
+                ts(2031, 1, 1), ts(2030, 12, 31, 23, 59, 59), ts(2026, 1, 1), ts(2025, 12, 31, 23, 59)]:
+        for back in [1, 59, 86400, 400 * 86400, 5 * 366 * 86400, 9 * 366 * 86400]:
+            got = shim.unmet(base, np.full(S, now - back), now)
+            want = po.batch_unmet(base, np.full(S, now - back), now)
+            _cmp(got, want, (now, back))
+    n = 20000
+    masks = synth.gen_specs(n, seed=5)
+    now = ts(2027, 12, 31, 23, 59, 30)
+    earliest = now - synth.gen_times(n, 0, 40 * 86400, seed=6)
+    _cmp(shim.unmet(masks, earliest, now), po.batch_unmet(masks, earliest, now))
+
+
+def every_batch(n=4000, seed=123):
+    """a mixed batch: SpecSchedules and ConstantDelaySchedules ("@every", EVERY_TAG encoding) side by side, with the
+    expected answers for the latter computed here in numpy (constantdelay.go: Next(t) = t + delay)"""
+    rng = np.random.default_rng(seed)
+    masks = synth.gen_specs(n, seed=seed, dense_minutes=0.3)
+    is_every = rng.random(n) < 0.4
+    delay = rng.choice([1, 7, 60, 90, 3600, 5400, 86400, 40 * 86400, 9_000_000_000], size=n).astype(np.int64)
+    masks[:, is_every] = 0
+    masks[3, is_every] = delay[is_every].astype(np.uint64)
+    masks[4, is_every] = np.uint64(1 << 62)
+    now = ts(2026, 3, 29, 12)
+    earliest = now - synth.gen_times(n, -3600, 3 * 86400, seed=seed)  # some after now
+    return masks, is_every, delay, earliest, now
+
+
+def test_every_schedules_in_mixed_batches():
+    masks, is_every, delay, earliest, now = every_batch()
+    n = masks.shape[1]
+    zid = np.where(np.arange(n) % 3 == 0, NAMES.index("Europe/Berlin"), 0).astype(np.int32)  # ignored by @every
+    for k in (1, 5):
+        got = shim.next_n(masks, earliest, k, zid)
+        want = po.batch_next_n(masks, earliest, k, zid, NAMES)
+        assert np.array_equal(got, want)
+        assert np.array_equal(got[is_every], earliest[is_every, None] + delay[is_every, None] * np.arange(1, k + 1))
+    rng = np.random.default_rng(1)
+    policy, active = rng.integers(0, 3, n).astype(np.uint8), rng.integers(0, 3, n).astype(np.uint32)
+    flags = (rng.random(n) < 0.05).astype(np.uint8)
+    got = shim.unmet(masks, earliest, now, 0, policy, active, flags, None, zid)
+    want = po.batch_unmet(masks, earliest, now, 0, policy, active, flags, None, zid, NAMES)
+    _cmp(got, want)
+    e = is_every & (flags == 0)
+    after = earliest > now
+    k = np.where(after, 0, (now - earliest) // delay)
+    assert np.array_equal(got["missed"][e], k[e].astype(np.uint32))
+    assert np.array_equal(got["next"][e], np.full(e.sum(), now) + delay[e])
+    assert np.array_equal(got["last"][e], np.where(k[e] > 0, earliest[e] + k[e] * delay[e], po.ZERO))
+    assert np.array_equal(got["status"][e], np.where(after[e], 2, 0))
+    # the parsers hand out the same encoding
+    for text, d in (("@every 90s", 90), ("@every 1h30m", 5400), ("@every 500ms", 1), ("TZ=Asia/Tokyo @every 2h", 7200)):
+        s, kind, every, _ = po.parse_standard(text)
+        assert (kind, every) == (1, d) and s.tuple() == (0, 0, 0, d, 1 << 62, 0)

@@ -45,8 +45,11 @@ def test_static_scratch_offsets_match_allocating_entry_point_twice_in_a_row():
             ctx.sync_check(stream=st)
             assert torch.cuda.mem_get_info()[0] >= free_before, "device memory was allocated during the calls"
             got = [o.cpu().numpy() for o in outs]
-            for g, w, (_, n, cap) in zip(got, want, inputs):
+            for g, w, ((missed, decision), n, cap) in zip(got, want, inputs):
                 assert np.array_equal(g, w), (n, cap)
+                # and against the definition itself: exclusive prefix sum of min(missed, cap) over listed decisions
+                cnt = np.where(decision.cpu().numpy() >= api.DEC_REQUEUE_ONLY, np.minimum(missed.cpu().numpy(), cap), 0)
+                assert np.array_equal(g, np.concatenate([[0], np.cumsum(cnt.astype(np.int64))])), (n, cap)
                 assert g[0] == 0 and np.all(np.diff(g) >= 0) and np.all(np.diff(g) <= cap)
             # n == 0 and the size limit
             off1 = torch.full((1,), -1, dtype=torch.int64, device="cuda")
