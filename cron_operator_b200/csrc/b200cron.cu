@@ -297,12 +297,12 @@ cudaError_t launch_unmet(b200cron_ctx* ctx, Device& d, cudaStream_t st, const Un
   return cudaEventRecord(b.done, st);
 }
 
-cudaError_t launch_history(b200cron_ctx* ctx, cudaStream_t st, const uint64_t* seg_off, const int64_t* key,
+cudaError_t launch_history(b200cron_ctx* ctx, const Device& d, cudaStream_t st, const uint64_t* seg_off, const int64_t* key,
                            const int64_t* limit, size_t nseg, uint32_t* perm, uint8_t* keep) {
   if (nseg == 0) return cudaSuccess;
   const unsigned grid = (unsigned)((nseg + kHistSegs - 1) / kHistSegs);
   ctx->launches.fetch_add(1, std::memory_order_relaxed);
-  history_prune_kernel<<<grid, kHistThreads, 0, st>>>(seg_off, key, limit, nseg, perm, keep);
+  history_prune_kernel<<<grid, kHistThreads, 0, st>>>(seg_off, key, limit, nseg, perm, keep, d.d_err);
   return cudaGetLastError();
 }
 
@@ -312,6 +312,8 @@ int check_err_flags(b200cron_ctx* ctx) {
     bits |= *d.h_err;
     *d.h_err = 0;
   }
+  if (bits & kErrSegLen)
+    return fail(ctx, B200CRON_EINVAL, "history_prune: a segment has more than %llu records", (unsigned long long)kHistMaxSeg);
   if (bits & kErrZone) return fail(ctx, B200CRON_ERANGE, "zone_id outside [0, %d)", (int)ctx->zones.names.size());
   if (bits & kErrRange)
     return fail(ctx, B200CRON_ERANGE,
@@ -489,6 +491,8 @@ extern "C" int b200cron_sync_check(b200cron_ctx* ctx, int dev_index, void* strea
   CU(ctx, cudaStreamSynchronize(st));
   const int bits = *d->h_err;
   *d->h_err = 0;
+  if (bits & kErrSegLen)
+    return fail(ctx, B200CRON_EINVAL, "history_prune: a segment has more than %llu records", (unsigned long long)kHistMaxSeg);
   if (bits & kErrZone) return fail(ctx, B200CRON_ERANGE, "zone_id outside [0, %d)", (int)ctx->zones.names.size());
   if (bits & kErrRange)
     return fail(ctx, B200CRON_ERANGE,
@@ -1199,7 +1203,7 @@ extern "C" int b200cron_history_prune_dev(b200cron_ctx* ctx, int dev_index, void
   if (!seg_off || (nrec && (!key || !perm || !keep))) return fail(ctx, B200CRON_EINVAL, "history_prune: NULL argument");
   std::lock_guard<std::mutex> lk(ctx->mu);
   CU(ctx, cudaSetDevice(d->id));
-  CU(ctx, launch_history(ctx, stream ? (cudaStream_t)stream : d->stream, seg_off, key, limit, nseg, perm, keep));
+  CU(ctx, launch_history(ctx, *d, stream ? (cudaStream_t)stream : d->stream, seg_off, key, limit, nseg, perm, keep));
   return B200CRON_OK;
 }
 
@@ -1208,8 +1212,12 @@ extern "C" int b200cron_history_prune(b200cron_ctx* ctx, const uint64_t* seg_off
   if (!ctx) return B200CRON_EINVAL;
   if (!seg_off) return fail(ctx, B200CRON_EINVAL, "history_prune: NULL seg_off");
   if (nseg == 0) return B200CRON_OK;
-  for (size_t s = 0; s < nseg; ++s)
+  for (size_t s = 0; s < nseg; ++s) {
     if (seg_off[s + 1] < seg_off[s]) return fail(ctx, B200CRON_EINVAL, "history_prune: seg_off must be non-decreasing");
+    if (seg_off[s + 1] - seg_off[s] > kHistMaxSeg)
+      return fail(ctx, B200CRON_EINVAL, "history_prune: segment %zu has %llu records (at most %llu per Cron)", s,
+                  (unsigned long long)(seg_off[s + 1] - seg_off[s]), (unsigned long long)kHistMaxSeg);
+  }
   const uint64_t nrec = seg_off[nseg] - seg_off[0];
   if (nrec && (!key || !perm || !keep)) return fail(ctx, B200CRON_EINVAL, "history_prune: NULL argument");
   std::lock_guard<std::mutex> lk(ctx->mu);
@@ -1242,7 +1250,7 @@ extern "C" int b200cron_history_prune(b200cron_ctx* ctx, const uint64_t* seg_off
     if (limit) CU(ctx, cudaMemcpyAsync(d_limit, limit + s0, ns * 8, cudaMemcpyHostToDevice, s.stream));
     if (nr) CU(ctx, cudaMemcpyAsync(d_key, key + r0, nr * 8, cudaMemcpyHostToDevice, s.stream));
     // the kernel addresses records by absolute offset: bias the record pointers by -r0
-    CU(ctx, launch_history(ctx, s.stream, d_off, d_key - r0, limit ? d_limit : nullptr, ns, d_perm - r0, d_keep - r0));
+    CU(ctx, launch_history(ctx, d, s.stream, d_off, d_key - r0, limit ? d_limit : nullptr, ns, d_perm - r0, d_keep - r0));
     if (nr) {
       CU(ctx, cudaMemcpyAsync(perm + r0, d_perm, nr * 4, cudaMemcpyDeviceToHost, s.stream));
       CU(ctx, cudaMemcpyAsync(keep + r0, d_keep, nr, cudaMemcpyDeviceToHost, s.stream));

@@ -20,7 +20,7 @@ constexpr int64_t kMinTime = -62135596800LL;
 constexpr int64_t kMaxTime = 253402300799LL;
 constexpr int64_t kSixYears = 6LL * 366 * 86400;
 
-enum : int { kErrRange = 1, kErrZone = 2 };
+enum : int { kErrRange = 1, kErrZone = 2, kErrSegLen = 4 };
 
 struct MaskPlanes {
   const uint64_t* p[6];
@@ -369,35 +369,40 @@ next1_ring_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64
   bool waited = false;
   int st = 0;
   uint32_t parity = 0;
-  for (size_t tile = g; tile < tiles; tile += W) {
-    mbar_wait(bar0 + 8u * st, parity);
-    const unsigned char* sp = my + st * kRingStageBytes;
-    const uint64_t* pl = reinterpret_cast<const uint64_t*>(sp) + lane;
-    const Spec s = cronwalk::make_spec(have_sec ? pl[0] : 1ULL, pl[32], pl[64], pl[96], pl[128], pl[160]);
-    const int64_t t = (int64_t)pl[192];
-    const int32_t zone = have_zone ? reinterpret_cast<const int32_t*>(sp + 7 * 256)[lane] : 0;
-    __syncwarp();  // every lane has taken its operands out of the stage: lane 0 may refill it
-    if (lane == 0 && tile + (size_t)kRingStages * W < tiles) fill(tile + (size_t)kRingStages * W, st);
-    if (++st == kRingStages) { st = 0; parity ^= 1u; }
+  // full tiles come through the ring; the n % 32 leftover specs form one more tile that is read with plain loads
+  // (same loop body, so the walk exists once in the instruction stream)
+  const size_t all_tiles = (n + 31) / 32;
+  for (size_t tile = g; tile < all_tiles; tile += W) {
+    const size_t i = tile * 32 + lane;
+    uint64_t mk[6];
+    int64_t t;
+    int32_t zone = 0;
+    if (tile < tiles) {  // warp-uniform
+      mbar_wait(bar0 + 8u * st, parity);
+      const unsigned char* sp = my + st * kRingStageBytes;
+      const uint64_t* pl = reinterpret_cast<const uint64_t*>(sp) + lane;
+      mk[0] = have_sec ? pl[0] : 1ULL;
+#pragma unroll
+      for (int p = 1; p < 6; ++p) mk[p] = pl[32 * p];
+      t = (int64_t)pl[192];
+      if (have_zone) zone = reinterpret_cast<const int32_t*>(sp + 7 * 256)[lane];
+      __syncwarp();  // every lane has taken its operands out of the stage: lane 0 may refill it
+      if (lane == 0 && tile + (size_t)kRingStages * W < tiles) fill(tile + (size_t)kRingStages * W, st);
+      if (++st == kRingStages) { st = 0; parity ^= 1u; }
+    } else {
+      const size_t ii = i < n ? i : n - 1;
+      mk[0] = have_sec ? __ldg(m.p[0] + ii) : 1ULL;
+#pragma unroll
+      for (int p = 1; p < 6; ++p) mk[p] = __ldg(m.p[p] + ii);
+      t = __ldg(from + ii);
+      if (have_zone) zone = __ldg(zone_id + ii);
+    }
+    const Spec s = cronwalk::make_spec(mk[0], mk[1], mk[2], mk[3], mk[4], mk[5]);
     Walk w;
     const bool ok = bind_checked(w, zt, zone, t, err);
     const int64_t r = ok ? cronwalk::next_from_t<false, kUtcOnly>(s, w, t, false) : kZero;
     if (!waited) { asm volatile("griddepcontrol.wait;" ::: "memory"); waited = true; }  // see next1_kernel
-    out[tile * 32 + lane] = r;
-  }
-  if (g == 0) {  // the n % 32 leftover specs
-    const size_t i = tiles * 32 + lane;
-    if (i < n) {
-      const Spec s = cronwalk::make_spec(have_sec ? __ldg(m.p[0] + i) : 1ULL, __ldg(m.p[1] + i), __ldg(m.p[2] + i),
-                                         __ldg(m.p[3] + i), __ldg(m.p[4] + i), __ldg(m.p[5] + i));
-      const int64_t t = __ldg(from + i);
-      const int32_t zone = have_zone ? __ldg(zone_id + i) : 0;
-      Walk w;
-      const bool ok = bind_checked(w, zt, zone, t, err);
-      const int64_t r = ok ? cronwalk::next_from_t<false, kUtcOnly>(s, w, t, false) : kZero;
-      if (!waited) { asm volatile("griddepcontrol.wait;" ::: "memory"); waited = true; }
-      out[i] = r;
-    }
+    if (i < n) out[i] = r;
   }
   if (!waited) asm volatile("griddepcontrol.wait;" ::: "memory");
 }
@@ -548,19 +553,16 @@ unmet_tile_kernel(UnmetArgs a, ZoneTable zt, int* __restrict__ err, uint32_t* __
                   uint32_t* __restrict__ defer_count) {
   const size_t base = (size_t)blockIdx.x * kUnmetTile;
   const int cnt = (int)((a.n - base) < (size_t)kUnmetTile ? (a.n - base) : (size_t)kUnmetTile);
-  if (a.zone_id == nullptr) {
-    for (int q = threadIdx.x; q < ((cnt + 31) & ~31); q += kUnmetThreads)
-      unmet_one<kUnmetUtc>(a, zt, err, base + q, q < cnt, nullptr, nullptr);
-    return;
-  }
   // deal the tile's Crons into the two classes: UTC indices packed from the front of s_idx, zoned ones from the back
+  // (a launch without zone ids is all UTC: identity order, no classification)
   __shared__ uint16_t s_idx[kUnmetTile];
   __shared__ int s_n[2];
-  if (threadIdx.x < 2) s_n[threadIdx.x] = 0;
+  if (threadIdx.x < 2) s_n[threadIdx.x] = threadIdx.x == 0 && a.zone_id == nullptr ? cnt : 0;
   __syncthreads();
   const unsigned lane = threadIdx.x & 31u;
 #pragma unroll
   for (int it = 0; it < kUnmetTile / kUnmetThreads; ++it) {
+    if (a.zone_id == nullptr) break;
     const int q = it * kUnmetThreads + threadIdx.x;
     const bool in = q < cnt;
     const bool zoned = in && __ldg(a.zone_id + base + q) != 0;
@@ -580,7 +582,7 @@ unmet_tile_kernel(UnmetArgs a, ZoneTable zt, int* __restrict__ err, uint32_t* __
   const int nu = s_n[0], nz = s_n[1];
   for (int q = threadIdx.x; q < ((nu + 31) & ~31); q += kUnmetThreads) {
     const bool live = q < nu;
-    unmet_one<kUnmetUtc>(a, zt, err, base + (live ? s_idx[q] : 0), live, nullptr, nullptr);
+    unmet_one<kUnmetUtc>(a, zt, err, base + (live ? (a.zone_id ? (int)s_idx[q] : q) : 0), live, nullptr, nullptr);
   }
   if (kZoned) {
     for (int q = threadIdx.x; q < ((nz + 31) & ~31); q += kUnmetThreads) {
@@ -704,87 +706,115 @@ zone_order_scatter_kernel(const int32_t* __restrict__ zone_id, size_t n, int32_t
 // history_prune: stable ascending order of each Cron's finished workloads by creation time + keep/delete flags
 //                                                           (cron_util.go:117-129, cron_controller.go:313-323)
 //
-// A CTA owns kHistSegs consecutive segments, i.e. one contiguous run of records.  The run's keys are brought into
-// shared memory with coalesced loads, every record finds its segment by binary search over the tile's offsets and
-// its stable rank by counting the records of its segment that sort before it (segments are short: the reference
-// keeps historyLimit of them), and perm/keep go straight to global memory (sector-coalesced, see below).
-// Runs longer than kHistCap records are ranked straight from global memory (L2-resident) -- correct for any
-// length, but quadratic in the segment length.
+// A CTA owns kHistSegs consecutive segments, i.e. one contiguous run of records, and works through it in chunks of
+// whole segments that fit kHistCap records (sized by records, not by segments: a tile of long histories simply takes
+// more chunks).  A chunk's keys are brought into shared memory with coalesced loads as 32-bit differences to the
+// chunk's first key (creation timestamps of one Cron's workloads lie within days of each other; a chunk whose keys
+// span more than 2^31 keeps them as 64-bit values), every record finds its segment through a one-byte stamp and its
+// stable rank by counting the records of its segment that sort before it (segments are short: the reference keeps
+// historyLimit of them), and perm/keep go straight to global memory (a warp's lanes hold consecutive records, so a
+// permutation inside a segment touches the same 32-byte sectors as the identity).
+// A single segment longer than kHistCap is ranked by the whole CTA straight from global memory -- quadratic, so
+// bounded: above kHistMaxSeg records the launch flags kErrSegLen (B200CRON_EINVAL) and leaves that segment in input
+// order with every record kept.
 // Algorithmic bytes: 8 (key) in, 4 (perm) + 1 (keep) out per record; 8 (offset) + 8 (limit) in per segment.
 // -------------------------------------------------------------------------------------------------------------
 constexpr int kHistThreads = 256;
 constexpr int kHistSegs = 256;
-constexpr int kHistCap = 3072;  // records per CTA tile held in shared memory (31 KB static with seg ids/offsets/limits)
+constexpr int kHistCap = 2048;          // records per chunk held in shared memory
+constexpr uint64_t kHistMaxSeg = 65536;  // longest segment the quadratic path will rank
 
 __global__ void __launch_bounds__(kHistThreads)
 history_prune_kernel(const uint64_t* __restrict__ seg_off, const int64_t* __restrict__ key,
                      const int64_t* __restrict__ limit, size_t nseg, uint32_t* __restrict__ perm,
-                     uint8_t* __restrict__ keep) {
+                     uint8_t* __restrict__ keep, int* __restrict__ err) {
   __shared__ uint64_t s_off[kHistSegs + 1];
-  __shared__ int64_t s_key[kHistCap];
+  __shared__ __align__(8) unsigned char s_keys[kHistCap * 8];  // int32 differences, or int64 keys for a wide chunk
+  __shared__ uint8_t s_seg[kHistCap];
+  __shared__ int32_t s_lim[kHistSegs];  // HistoryLimit clamped to 31 bits; nil (negative) = keep everything
   const size_t seg0 = (size_t)blockIdx.x * kHistSegs;
   const int nsegs = (int)((nseg - seg0) < (size_t)kHistSegs ? (nseg - seg0) : (size_t)kHistSegs);
   for (int x = threadIdx.x; x <= nsegs; x += kHistThreads) s_off[x] = __ldg(seg_off + seg0 + x);
+  for (int x = threadIdx.x; x < nsegs; x += kHistThreads) {
+    const int64_t lim = limit ? __ldg(limit + seg0 + x) : -1;
+    s_lim[x] = (lim < 0 || lim > 0x7fffffff) ? 0x7fffffff : (int32_t)lim;
+  }
   __syncthreads();
-  const uint64_t r0 = s_off[0];
-  const uint64_t total = s_off[nsegs] - r0;
-  const bool in_smem = total <= (uint64_t)kHistCap;
-  if (in_smem) {
-    for (uint32_t x = threadIdx.x; x < total; x += kHistThreads) s_key[x] = __ldg(key + r0 + x);
-    __syncthreads();
-  }
-  if (in_smem) {
-    // Shared-memory path, all 32-bit.  Each segment's thread stamps its id over its own records (segments are
-    // short), so a record finds its segment with one load instead of a binary search over the offsets.
-    __shared__ uint8_t s_seg[kHistCap];
-    __shared__ uint32_t s_rel[kHistSegs + 1];
-    __shared__ int32_t s_lim[kHistSegs];
-    const uint32_t tot = (uint32_t)total;
-    for (int sg = threadIdx.x; sg <= nsegs; sg += kHistThreads) s_rel[sg] = (uint32_t)(s_off[sg] - r0);
-    for (int sg = threadIdx.x; sg < nsegs; sg += kHistThreads) {
-      const int64_t lim = limit ? __ldg(limit + seg0 + sg) : -1;
-      s_lim[sg] = (lim < 0 || lim > (int64_t)kHistCap) ? (int32_t)kHistCap : (int32_t)lim;  // >= len keeps everything
-      const uint32_t a0 = (uint32_t)(s_off[sg] - r0), b0 = (uint32_t)(s_off[sg + 1] - r0);
-      for (uint32_t j = a0; j < b0; ++j) s_seg[j] = (uint8_t)sg;
-    }
-    __syncthreads();
-    for (uint32_t x = threadIdx.x; x < tot; x += kHistThreads) {
-      const int sg = s_seg[x];
-      const uint32_t a = s_rel[sg], b = s_rel[sg + 1];
-      const int64_t kx = s_key[x];
-      uint32_t rank = 0;
-      for (uint32_t j = a; j < b; ++j) {
-        const int64_t kj = s_key[j];
-        rank += (kj < kx) || (kj == kx && j < x);
-      }
-      // sorted position `rank` is deleted when rank < len - limit.  Written straight to global memory: the lanes of a
-      // warp hold consecutive records, i.e. a handful of whole segments, and a permutation inside a segment touches
-      // the same 32-byte sectors as the identity would -- staging the outputs in shared memory bought nothing and
-      // cost 15 KB per CTA (4 resident CTAs per SM instead of 7).
-      perm[r0 + a + rank] = x - a;
-      keep[r0 + a + rank] = !((int32_t)rank < (int32_t)(b - a) - s_lim[sg]);
-    }
-    return;
-  }
-  // Long runs (more than kHistCap records in the tile): rank straight from global memory.
-  for (uint64_t x = threadIdx.x; x < total; x += kHistThreads) {
-    int lo = 0, hi = nsegs;  // largest sg with s_off[sg] - r0 <= x
+  int32_t* k32 = reinterpret_cast<int32_t*>(s_keys);
+  int64_t* k64 = reinterpret_cast<int64_t*>(s_keys);
+  int sa = 0;
+  while (sa < nsegs) {  // every thread computes the same chunk boundaries from shared memory
+    const uint64_t r0 = s_off[sa];
+    int lo = sa, hi = nsegs + 1;  // largest sb in (sa, nsegs] with s_off[sb] - r0 <= kHistCap, at least sa + 1
     while (hi - lo > 1) {
       const int mid = (lo + hi) >> 1;
-      if (s_off[mid] - r0 <= x) lo = mid; else hi = mid;
+      if (s_off[mid] - r0 <= (uint64_t)kHistCap) lo = mid; else hi = mid;
     }
-    const uint64_t a = s_off[lo] - r0, b = s_off[lo + 1] - r0;
-    const uint64_t len = b - a;
-    const int64_t kx = __ldg(key + r0 + x);
-    uint32_t rank = 0;
-    for (uint64_t j = a; j < b; ++j) {
-      const int64_t kj = __ldg(key + r0 + j);
-      rank += (kj < kx) || (kj == kx && j < x);
+    if (lo == sa) {
+      // ---- one segment longer than a chunk: ranked by the whole CTA from global memory ----
+      const uint64_t len = s_off[sa + 1] - r0;
+      const int64_t lim = limit ? __ldg(limit + seg0 + sa) : -1;
+      if (len > kHistMaxSeg) {
+        if (threadIdx.x == 0) atomicOr(err, kErrSegLen);
+        for (uint64_t x = threadIdx.x; x < len; x += kHistThreads) { perm[r0 + x] = (uint32_t)x; keep[r0 + x] = 1; }
+      } else {
+        for (uint64_t x = threadIdx.x; x < len; x += kHistThreads) {
+          const int64_t kx = __ldg(key + r0 + x);
+          uint32_t rank = 0;
+          for (uint64_t j = 0; j < len; ++j) {
+            const int64_t kj = __ldg(key + r0 + j);
+            rank += (kj < kx) || (kj == kx && j < x);
+          }
+          perm[r0 + rank] = (uint32_t)x;
+          keep[r0 + rank] = (lim < 0) ? 1 : !((int64_t)rank < (int64_t)len - lim);
+        }
+      }
+      sa += 1;
+      continue;
     }
-    const int64_t lim = limit ? __ldg(limit + seg0 + lo) : -1;
-    // sorted position `rank` is deleted when rank < len - limit (limit < 0: HistoryLimit nil keeps everything)
-    perm[r0 + a + rank] = (uint32_t)(x - a);
-    keep[r0 + a + rank] = (lim < 0) ? 1 : !((int64_t)rank < (int64_t)len - lim);
+    const int sb = lo;
+    const uint32_t tot = (uint32_t)(s_off[sb] - r0);
+    // ---- load the chunk: keys as 32-bit differences when they all fit, segment stamps ----
+    __syncthreads();  // the previous chunk's readers are done with s_keys / s_seg
+    const int64_t base = tot ? __ldg(key + r0) : 0;
+    bool wide = false;
+    for (uint32_t x = threadIdx.x; x < tot; x += kHistThreads) {
+      const int64_t d = __ldg(key + r0 + x) - base;  // wraps for absurd spans; caught by the check on the stored value
+      k32[x] = (int32_t)d;
+      wide = wide || d != (int64_t)(int32_t)d || (__ldg(key + r0 + x) < base) != (d < 0);
+    }
+    for (int sg = sa + threadIdx.x; sg < sb; sg += kHistThreads) {
+      const uint32_t a0 = (uint32_t)(s_off[sg] - r0), b0 = (uint32_t)(s_off[sg + 1] - r0);
+      for (uint32_t j = a0; j < b0; ++j) s_seg[j] = (uint8_t)(sg - sa);
+    }
+    const bool any_wide = __syncthreads_or(wide);
+    if (any_wide) {  // keys too far apart for 32 bits: reload them whole
+      for (uint32_t x = threadIdx.x; x < tot; x += kHistThreads) k64[x] = __ldg(key + r0 + x);
+      __syncthreads();
+    }
+    for (uint32_t x = threadIdx.x; x < tot; x += kHistThreads) {
+      const int sg = sa + s_seg[x];
+      const uint32_t a = (uint32_t)(s_off[sg] - r0), b = (uint32_t)(s_off[sg + 1] - r0);
+      uint32_t rank = 0;
+      if (!any_wide) {
+        const int32_t kx = k32[x];
+#pragma unroll 4
+        for (uint32_t j = a; j < b; ++j) {
+          const int32_t kj = k32[j];
+          rank += (kj < kx) | ((kj == kx) & (j < x));
+        }
+      } else {
+        const int64_t kx = k64[x];
+        for (uint32_t j = a; j < b; ++j) {
+          const int64_t kj = k64[j];
+          rank += (kj < kx) || (kj == kx && j < x);
+        }
+      }
+      // sorted position `rank` is deleted when rank < len - limit
+      perm[r0 + a + rank] = x - a;
+      keep[r0 + a + rank] = !((int64_t)rank < (int64_t)(b - a) - (int64_t)s_lim[sg]);
+    }
+    sa = sb;
   }
 }
 
@@ -794,7 +824,7 @@ history_prune_kernel(const uint64_t* __restrict__ seg_off, const int64_t* __rest
 //
 // list_off = exclusive prefix sum of the per-Cron counts (three small kernels: per-tile sums into a scratch array,
 // a single-CTA scan of the tile sums, per-tile offsets = warp-shuffle scan + tile base); unmet_list_emit_kernel then
-// re-walks each chain and writes its fire times at list + list_off[i].  Gated / unschedulable Crons contribute 0.
+// re-walks each chain and writes its fire times at list + list_off[i] (through a per-warp tile, see below).  Gated / unschedulable Crons contribute 0.
 // Scratch: one uint64 per tile of kScanTile Crons.
 // -------------------------------------------------------------------------------------------------------------
 constexpr int kScanThreads = 256;
@@ -894,24 +924,49 @@ list_offsets_kernel(const uint32_t* __restrict__ missed, const uint8_t* __restri
   if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) list_off[n] = tile_sums[gridDim.x];
 }
 
+// Warp-cooperative emission: a warp owns 32 consecutive Crons, whose lists are one contiguous run of the output.  The
+// run is produced window by window: every lane walks its own chain and drops the fire times that fall into the current
+// window into the warp's shared-memory tile (at their final position), then the warp writes the window out with
+// lane-consecutive stores -- full 256-byte rows instead of 32 separate 8-byte streams 800 bytes apart.
+constexpr int kEmitWindow = 512;  // list entries per window (4 KB per warp)
 __global__ void __launch_bounds__(kUnmetThreads)
 unmet_list_emit_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* __restrict__ earliest,
                        size_t n, const uint64_t* __restrict__ list_off, int64_t* __restrict__ list, ZoneTable zt) {
-  const size_t i = (size_t)blockIdx.x * kUnmetThreads + threadIdx.x;
-  if (i >= n) return;
-  const uint64_t a = __ldg(list_off + i), b = __ldg(list_off + i + 1);
-  if (b == a) return;
-  const Spec s = cronwalk::make_spec(m.p[0] ? __ldg(m.p[0] + i) : 1ULL, __ldg(m.p[1] + i), __ldg(m.p[2] + i),
-                                     __ldg(m.p[3] + i), __ldg(m.p[4] + i), __ldg(m.p[5] + i));
-  const int32_t zone = zone_id ? __ldg(zone_id + i) : 0;
+  __shared__ int64_t s_tile[kUnmetThreads / 32][kEmitWindow];
+  const unsigned lane = threadIdx.x & 31u;
+  int64_t* tile = s_tile[threadIdx.x >> 5];
+  const size_t i0 = (size_t)blockIdx.x * kUnmetThreads + (threadIdx.x & ~31u);
+  if (i0 >= n) return;  // warp-uniform
+  const size_t i = i0 + lane;
+  const bool live = i < n;
+  const size_t ii = live ? i : n - 1;
+  const uint64_t a = live ? __ldg(list_off + ii) : 0, b = live ? __ldg(list_off + ii + 1) : 0;
+  const size_t ilast = (i0 + 31 < n) ? i0 + 31 : n - 1;
+  const uint64_t run_lo = __ldg(list_off + i0), run_hi = __ldg(list_off + ilast + 1);
+  if (run_hi == run_lo) return;  // warp-uniform: nothing listed for these 32 Crons
+  const Spec s = cronwalk::make_spec(m.p[0] ? __ldg(m.p[0] + ii) : 1ULL, __ldg(m.p[1] + ii), __ldg(m.p[2] + ii),
+                                     __ldg(m.p[3] + ii), __ldg(m.p[4] + ii), __ldg(m.p[5] + ii));
+  const int32_t zone = zone_id ? __ldg(zone_id + ii) : 0;
   Walk w;
   if (zone == 0) w.bind_utc(); else w.bind_zone(zt, zone);  // ids and ranges were validated by the unmet kernels
-  int64_t t = __ldg(earliest + i);
+  int64_t t = __ldg(earliest + ii);
   bool resident = false;
-  for (uint64_t j = a; j < b; ++j) {
-    t = cronwalk::next_from_t<true>(s, w, t, resident);
-    resident = true;
-    list[j] = t;
+  uint64_t j = a;
+  for (uint64_t win = run_lo; win < run_hi; win += kEmitWindow) {
+    const uint64_t wend = (run_hi - win) < (uint64_t)kEmitWindow ? run_hi : win + kEmitWindow;
+    for (;;) {  // one chained call per round; the vote is the reconvergence point
+      const bool go = j < b && j < wend;
+      if (!__any_sync(0xffffffffu, go)) break;
+      if (go) {
+        t = cronwalk::next_from_t<true>(s, w, t, resident);
+        resident = true;
+        tile[j - win] = t;
+        ++j;
+      }
+    }
+    __syncwarp();
+    for (uint64_t x = lane; x < wend - win; x += 32) list[win + x] = tile[x];
+    __syncwarp();
   }
 }
 

@@ -255,7 +255,11 @@ int b200cron_unmet_since_set(b200cron_ctx* ctx, const b200cron_specset* set, con
  * key[] (creation timestamps; any int64 key works).  limit[s] = Spec.HistoryLimit, negative = nil (keep all);
  * limit == NULL keeps all.  Outputs, per record position p inside its segment's sorted order:
  *   perm[seg_off[s] + p] = index inside the segment of the record that sorts p-th (stable, ascending);
- *   keep[seg_off[s] + p] = 0 when that record is deleted (p < len - limit), 1 when it stays in Status.History. */
+ *   keep[seg_off[s] + p] = 0 when that record is deleted (p < len - limit), 1 when it stays in Status.History.
+ * Segments are expected to be short (the reference keeps HistoryLimit records per Cron): up to 2,048 records a
+ * segment is ranked in shared memory, up to 65,536 by a quadratic pass over global memory, and a longer one is
+ * rejected (B200CRON_EINVAL; the _dev form reports it at the next b200cron_sync_check and leaves that segment in
+ * input order, everything kept). */
 int b200cron_history_prune(b200cron_ctx* ctx, const uint64_t* seg_off, const int64_t* key, const int64_t* limit,
                            size_t nseg, uint32_t* perm, uint8_t* keep);
 int b200cron_history_prune_dev(b200cron_ctx* ctx, int dev_index, void* stream, const uint64_t* seg_off,

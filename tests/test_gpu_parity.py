@@ -738,3 +738,40 @@ def test_C4_full_size_sampled_parity(ctx, names):
     assert bool(((nxt > now) | ~live).all()) and bool(((last <= now) | (last == po.ZERO)).all())
     assert bool(((miss > 0) == ((last != po.ZERO) & live))[live].all())
     assert bool(((dec == api.DEC_REQUEUE_ONLY) == (live & (last == po.ZERO)))[live].all())
+
+
+def test_history_chunking_wide_keys_and_length_limit(ctx):
+    """history_prune works through a tile in chunks of whole segments (sized by records), keeps 64-bit keys when a
+    chunk's keys do not fit 32-bit differences, ranks a long segment from global memory and rejects an absurd one"""
+    import torch
+    rng = np.random.default_rng(19)
+    for nseg, maxlen, wide in [(700, 60, False), (5, 2500, False), (300, 16, True), (40, 300, True), (2, 20_000, False)]:
+        lens = rng.integers(0, maxlen + 1, nseg)
+        seg_off = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+        m = int(seg_off[-1])
+        if wide:  # nanosecond-like and full-range keys, with ties
+            key = rng.integers(-2**62, 2**62, m, dtype=np.int64)
+            key[rng.random(m) < 0.3] = key[0] if m else 0
+        else:
+            key = (1_700_000_000 - rng.integers(0, 500, m)).astype(np.int64)
+        for limit in (None, rng.integers(-1, 30, nseg).astype(np.int64), np.full(nseg, 2**40, np.int64)):
+            perm, keep = ctx.history_prune(seg_off, key, limit)
+            wperm, wkeep = po.batch_history(seg_off, key, limit)
+            assert np.array_equal(perm, wperm) and np.array_equal(keep, wkeep), (nseg, maxlen, wide)
+    seg_off = np.array([0, 3, 3 + 65_537, 3 + 65_537 + 2], np.uint64)
+    key = rng.integers(0, 1000, int(seg_off[-1])).astype(np.int64)
+    with pytest.raises(api.B200CronError) as e:
+        ctx.history_prune(seg_off, key, None)
+    assert e.value.code == api.EINVAL and "65536" in str(e.value)
+    st = torch.cuda.current_stream().cuda_stream
+    ds, dk = torch.from_numpy(seg_off.view(np.int64)).cuda(), torch.from_numpy(key).cuda()
+    perm = torch.empty(len(key), dtype=torch.int32, device="cuda")
+    keep = torch.empty(len(key), dtype=torch.uint8, device="cuda")
+    ctx.history_prune_dev(ds, dk, None, perm, keep, stream=st)
+    with pytest.raises(api.B200CronError) as e:
+        ctx.sync_check(stream=st)
+    assert e.value.code == api.EINVAL
+    p = perm.cpu().numpy()
+    assert np.array_equal(p[3:3 + 65_537], np.arange(65_537)) and bool((keep[3:3 + 65_537] == 1).all())  # left as is
+    w0, _ = po.history_prune(key[:3], None)
+    assert np.array_equal(p[:3].view(np.uint32), w0)                                                     # neighbours fine
