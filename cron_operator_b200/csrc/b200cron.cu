@@ -27,7 +27,8 @@ namespace {
 using namespace b200cron;
 
 constexpr int kSlots = 3;
-constexpr size_t kChunk = 1u << 18;  // specs per pipelined chunk of the host-pointer calls
+constexpr size_t kChunk = 1u << 18;       // specs per pipelined chunk of the host-pointer next_n calls
+constexpr size_t kUnmetChunk = 1u << 20;  // Crons per chunk of the host-pointer unmet calls (six launches per chunk)
 
 // Error text of the calling thread's last failed call: entry points validate their arguments before they take the
 // context's mutex, and callers on different threads (cgo runs Reconcile on up to MaxConcurrentReconciles OS threads)
@@ -163,9 +164,13 @@ cudaError_t launch_next_kt(bool vec, unsigned grid, size_t smem, cudaStream_t st
 }
 
 // B200CRON_NEXT1_RING (tuning builds): 1 = k == 1 launches on device-resident inputs use the persistent kernel with the
-// asynchronous input ring (next1_ring_kernel); 0 = always next1_kernel.
+// asynchronous input ring (next1_ring_kernel); 0 = always next1_kernel.  Measured on B200 (profiles/README.md, r2c):
+// the ring is bit-exact through the whole GPU suite but SLOWER -- 18.8 vs 13.7 us per 1M specs with overlapping
+// launches, 24.6 vs 18.5 us without -- because next1 is bound by instruction issue, not by load latency, and the
+// producer lane's bookkeeping (expect_tx + seven bulk copies per 32-spec tile, mbarrier waits) costs issue slots that
+// the plain kernel's seven LDGs do not.  So it is off, and compiled only into tuning builds.
 #ifndef B200CRON_NEXT1_RING
-#define B200CRON_NEXT1_RING 1
+#define B200CRON_NEXT1_RING 0
 #endif
 
 // device_resident: every buffer lives in this device's memory (the bulk-copy ring reads this GPU's memory only;
@@ -189,7 +194,8 @@ cudaError_t launch_next(b200cron_ctx* ctx, const Device& d, cudaStream_t st, con
     attr.val.programmaticStreamSerializationAllowed = 1;
     if (ctx->overlap.load(std::memory_order_relaxed)) { cfg.attrs = &attr; cfg.numAttrs = 1; }
     int* err = d.d_err;
-    if (B200CRON_NEXT1_RING && device_resident && vec && (!zone || aligned16(zone)) && n >= 32) {
+#if B200CRON_NEXT1_RING
+    if (device_resident && vec && (!zone || aligned16(zone)) && n >= 32) {
       const size_t cta_tiles = (n / 32 + kRingWarps - 1) / kRingWarps;
       const size_t resident = (size_t)d.sm_count * B200CRON_RING_MINBLOCKS;
       cfg.gridDim = dim3((unsigned)(cta_tiles < resident ? cta_tiles : resident));
@@ -198,6 +204,9 @@ cudaError_t launch_next(b200cron_ctx* ctx, const Device& d, cudaStream_t st, con
       if (zone) return cudaLaunchKernelEx(&cfg, next1_ring_kernel<false>, m, zone, from, n, out, d.zt, err);
       return cudaLaunchKernelEx(&cfg, next1_ring_kernel<true>, m, zone, from, n, out, d.zt, err);
     }
+#else
+    (void)device_resident;
+#endif
     if (zone) return cudaLaunchKernelEx(&cfg, next1_kernel<false>, m, zone, from, n, out, d.zt, err);
     return cudaLaunchKernelEx(&cfg, next1_kernel<true>, m, zone, from, n, out, d.zt, err);  // all-UTC launch
   }
@@ -640,37 +649,10 @@ extern "C" int b200cron_unmet_since(b200cron_ctx* ctx, const uint64_t* const mas
     if (!masks[p]) return fail(ctx, B200CRON_EINVAL, "unmet_since: only the seconds plane (masks[0]) may be NULL");
   std::lock_guard<std::mutex> lk(ctx->mu);
   const int G = (int)ctx->devs.size();
-  {  // zero-copy when every buffer is pinned host memory (see b200cron_next_n)
-    const void* req[] = {masks[1], masks[2], masks[3], masks[4], masks[5], earliest, last, next, missed, status, decision};
-    const void* opt[] = {masks[0], zone_id, policy, active, flags, deadline};
-    bool pinned = n > 0;
-    for (const void* q : req) pinned = pinned && q && is_pinned_host(q);
-    for (const void* q : opt) pinned = pinned && (!q || is_pinned_host(q));
-    if (pinned) {
-      for (int g = 0; g < G; ++g) {
-        Device& d = ctx->devs[g];
-        const Shard sh = shard_of(n, g, G);
-        if (sh.hi <= sh.lo) continue;
-        CU(ctx, cudaSetDevice(d.id));
-        UnmetArgs a{};
-        for (int p = 0; p < 6; ++p) a.m.p[p] = masks[p] ? dev_alias(masks[p]) + sh.lo : nullptr;
-        a.zone_id = zone_id ? dev_alias(zone_id) + sh.lo : nullptr;
-        a.earliest = dev_alias(earliest) + sh.lo; a.now = now; a.now_nsec = now_nsec;
-        a.policy = policy ? dev_alias(policy) + sh.lo : nullptr; a.active = active ? dev_alias(active) + sh.lo : nullptr;
-        a.flags = flags ? dev_alias(flags) + sh.lo : nullptr; a.deadline = deadline ? dev_alias(deadline) + sh.lo : nullptr;
-        a.n = sh.hi - sh.lo;
-        a.last = dev_alias(last) + sh.lo; a.next = dev_alias(next) + sh.lo; a.missed = dev_alias(missed) + sh.lo;
-        a.status = dev_alias(status) + sh.lo; a.decision = dev_alias(decision) + sh.lo;
-        CU(ctx, launch_unmet(ctx, d, d.stream, a));
-        CU(ctx, collect_err(d, d.stream));
-      }
-      for (Device& d : ctx->devs) {
-        CU(ctx, cudaSetDevice(d.id));
-        CU(ctx, cudaStreamSynchronize(d.stream));
-      }
-      return check_err_flags(ctx);
-    }
-  }
+  // Always staged, even from pinned buffers: the unmet kernels gather their inputs through index lists (class-pure and
+  // zone-ordered warps) and scatter their results, 8 bytes at a time -- patterns that crawl when every access is a PCIe
+  // transaction (measured: 296 ms per 10M Crons in place vs the copies' ~20 ms).  Pinned buffers still pay off: the
+  // chunk copies below are then truly asynchronous and run at full PCIe rate.
   // staging: 6 planes | earliest | deadline | last | next  (8 B) | zone | active | missed (4 B) | policy flags status decision (1 B)
   const size_t per_spec = 10 * 8 + 3 * 4 + 4;
   for (int g = 0; g < G; ++g) {
@@ -679,7 +661,7 @@ extern "C" int b200cron_unmet_since(b200cron_ctx* ctx, const uint64_t* const mas
     if (sh.hi <= sh.lo) continue;
     CU(ctx, cudaSetDevice(d.id));
     const size_t len = sh.hi - sh.lo;
-    const size_t chunk = std::min(kChunk, align_up(len, 2));
+    const size_t chunk = std::min(kUnmetChunk, align_up(len, 2));
     const size_t stride = align_up(chunk, 64);
     for (Slot& s : d.slots) {
       int rc = ensure_slot(ctx, s, stride * per_spec + 1024);
@@ -934,11 +916,7 @@ extern "C" int b200cron_unmet_since_set(b200cron_ctx* ctx, const b200cron_specse
     return fail(ctx, B200CRON_EINVAL, "unmet_since_set: NULL required argument");
   std::lock_guard<std::mutex> lk(ctx->mu);
   const int G = (int)ctx->devs.size();
-  const void* req[] = {earliest, last, next, missed, status, decision};
-  const void* opt[] = {policy, active, flags, deadline};
-  bool pinned = true;
-  for (const void* q : req) pinned = pinned && is_pinned_host(q);
-  for (const void* q : opt) pinned = pinned && (!q || is_pinned_host(q));
+  // always staged, pinned buffers or not: see b200cron_unmet_since
   // staging: earliest | deadline | last | next (8 B) | active | missed (4 B) | policy flags status decision (1 B)
   const size_t per_spec = 4 * 8 + 2 * 4 + 4;
   for (int g = 0; g < G; ++g) {
@@ -948,19 +926,7 @@ extern "C" int b200cron_unmet_since_set(b200cron_ctx* ctx, const b200cron_specse
     CU(ctx, cudaSetDevice(d.id));
     UnmetArgs a{};
     a.now = now; a.now_nsec = now_nsec;
-    if (pinned) {
-      a.m = set_planes(set, p, 0);
-      a.zone_id = p.zone;
-      a.earliest = dev_alias(earliest) + p.lo;
-      a.policy = policy ? dev_alias(policy) + p.lo : nullptr; a.active = active ? dev_alias(active) + p.lo : nullptr;
-      a.flags = flags ? dev_alias(flags) + p.lo : nullptr; a.deadline = deadline ? dev_alias(deadline) + p.lo : nullptr;
-      a.n = p.hi - p.lo;
-      a.last = dev_alias(last) + p.lo; a.next = dev_alias(next) + p.lo; a.missed = dev_alias(missed) + p.lo;
-      a.status = dev_alias(status) + p.lo; a.decision = dev_alias(decision) + p.lo;
-      CU(ctx, launch_unmet(ctx, d, d.stream, a));
-      continue;
-    }
-    const size_t chunk = std::min(kChunk, align_up(p.hi - p.lo, 2));
+    const size_t chunk = std::min(kUnmetChunk, align_up(p.hi - p.lo, 2));
     const size_t stride = align_up(chunk, 64);
     for (Slot& s : d.slots) {
       int rc = ensure_slot(ctx, s, stride * per_spec + 1024);
@@ -999,8 +965,7 @@ extern "C" int b200cron_unmet_since_set(b200cron_ctx* ctx, const b200cron_specse
   }
   for (Device& d : ctx->devs) {
     CU(ctx, cudaSetDevice(d.id));
-    if (!pinned)
-      for (Slot& s : d.slots) CU(ctx, cudaStreamSynchronize(s.stream));
+    for (Slot& s : d.slots) CU(ctx, cudaStreamSynchronize(s.stream));
     CU(ctx, collect_err(d, d.stream));
     CU(ctx, cudaStreamSynchronize(d.stream));
   }

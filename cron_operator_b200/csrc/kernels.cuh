@@ -181,6 +181,9 @@ constexpr int kNextTileSpecs = 512;
 #ifndef B200CRON_NEXTN_UTC_MINBLOCKS
 #define B200CRON_NEXTN_UTC_MINBLOCKS 10
 #endif
+#ifndef B200CRON_NEXTN_PAIR
+#define B200CRON_NEXTN_PAIR 1
+#endif
 #ifndef B200CRON_NEXTN_ZONED_MINBLOCKS
 #define B200CRON_NEXTN_ZONED_MINBLOCKS 6
 #endif
@@ -226,6 +229,9 @@ next_n_tile_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int6
     if (!live) w.bind_utc();
     if (!ss.never) w.tod_last = cronwalk::spec_tod_last(ss);  // lets chained calls skip exhausted days
     int64_t* row = out + i * (size_t)k;
+    // compile-time even k and a 16-byte aligned output: results leave two at a time (half the store instructions)
+    const bool pair = B200CRON_NEXTN_PAIR && KT > 0 && (KT & 1) == 0 && (reinterpret_cast<uintptr_t>(out) & 15u) == 0;
+    int64_t held = kZero;
 #pragma unroll 1
     for (int j = 0; j < k; ++j) {
       __syncwarp();  // every lane runs exactly k iterations: re-converge, or lanes on a short path run ahead for good
@@ -235,7 +241,12 @@ next_n_tile_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int6
       } else {
         t = kZero;
       }
-      if (live) row[j] = t;
+      if (pair) {
+        if (j & 1) { if (live) *reinterpret_cast<longlong2*>(row + j - 1) = make_longlong2(held, t); }
+        else held = t;
+      } else if (live) {
+        row[j] = t;
+      }
     }
   }
 }
@@ -292,6 +303,7 @@ next1_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* _
 // Bulk copies read THIS GPU's global memory only (the host passes device-resident buffers; pinned host buffers take
 // next1_kernel).  The n % 32 leftover specs are walked by warp 0 with plain loads.
 // -------------------------------------------------------------------------------------------------------------
+#if defined(B200CRON_NEXT1_RING) && B200CRON_NEXT1_RING
 #ifndef B200CRON_RING_STAGES
 #define B200CRON_RING_STAGES 2
 #endif
@@ -406,6 +418,7 @@ next1_ring_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64
   }
   if (!waited) asm volatile("griddepcontrol.wait;" ::: "memory");
 }
+#endif  // B200CRON_NEXT1_RING
 
 // -------------------------------------------------------------------------------------------------------------
 // unmet_since: getNextSchedule + gates + decision per Cron                    (cron_controller.go:163-220, 389-437)

@@ -188,6 +188,7 @@ parse_batch_kernel(const char* __restrict__ text, const uint64_t* __restrict__ t
           const bool unit_ends = k >= s.n || (ch(s, k) >= '0' && ch(s, k) <= '9');  // the unit is this one letter
           if (!unit_ends || !(u == 'h' || u == 'm' || u == 's')) { simple = false; break; }
           total += v * (u == 'h' ? 3600ULL : u == 'm' ? 60ULL : 1ULL);
+          if (total > 9000000000ULL) { simple = false; break; }  // near Go's 2^63 ns: the host parser decides
         }
         if (simple) {  // constantdelay.go Every(): at least one second
           m[3] = total < 1 ? 1 : total;
