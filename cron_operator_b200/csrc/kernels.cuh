@@ -474,10 +474,16 @@ constexpr int kUnmetEasyRounds = B200CRON_UNMET_EASY_ROUNDS;
 #endif
 
 // one Cron per lane; all 32 lanes of the warp must call this together (live = false for padding lanes)
+// kUnmetUtc takes a clock shift: `shift` = 0 for a Cron evaluated in UTC, or the UTC offset of the ONE zone period that
+// holds the Cron's whole window (class A of unmet_tile_kernel) -- inside a period local time is UTC moved by the offset,
+// so the UTC machine runs on the local clock and the answers are moved back.  `nhi` bounds the period's natural window
+// on that clock: a Next() beyond it (or one that found nothing in five years) left the period, the lane is then
+// *rejected -- nothing is written -- and the caller hands the Cron to the general path.
 template <int kMode>
 __device__ __forceinline__ void unmet_one(const UnmetArgs& a, const ZoneTable& zt, int* __restrict__ err, size_t i,
                                           bool live, uint32_t* __restrict__ defer_idx,
-                                          uint32_t* __restrict__ defer_count) {
+                                          uint32_t* __restrict__ defer_count, int32_t shift = 0,
+                                          int64_t nhi = cronwalk::kOmega, bool* rejected = nullptr) {
   const size_t ii = live ? i : 0;  // out-of-range lanes stay in the warp-uniform loop below, doing nothing
   // masks[0] == NULL: 5-field schedules, second 0 (what ParseStandard always yields)
   const Spec s = cronwalk::make_spec(a.m.p[0] ? __ldg(a.m.p[0] + ii) : 1ULL, __ldg(a.m.p[1] + ii), __ldg(a.m.p[2] + ii),
@@ -508,8 +514,17 @@ __device__ __forceinline__ void unmet_one(const UnmetArgs& a, const ZoneTable& z
   st.done = true;
   st.w.bind_utc();
   if (ok) {
-    if (s.every) st.o = cronwalk::unmet_decide_every((int64_t)s.second, in);  // "@every <dur>": closed form, no walk
-    else cronwalk::unmet_begin(zt, zone, in, st);
+    if (s.every) {
+      st.o = cronwalk::unmet_decide_every((int64_t)s.second, in);  // "@every <dur>": closed form, no walk
+    } else if (kMode == kUnmetUtc) {
+      st.o.decision = cronwalk::unmet_gate(in);  // the gates look at the real clock
+      if (st.o.decision == 0) {
+        in.earliest += shift; in.now += shift; in.deadline = kZero; in.flags = 0;
+        cronwalk::unmet_begin(zt, 0, in, st);
+      }
+    } else {
+      cronwalk::unmet_begin(zt, zone, in, st);
+    }
   }
   // all 32 lanes go round together: a full-mask vote per iteration is the reconvergence point
   bool defer = false;
@@ -517,6 +532,15 @@ __device__ __forceinline__ void unmet_one(const UnmetArgs& a, const ZoneTable& z
     while (__any_sync(0xffffffffu, !st.done)) {
       if (!st.done) cronwalk::unmet_step_utc(s, in, st);
     }
+    if (shift != 0 || nhi != cronwalk::kOmega) {  // a zoned lane: did every call stay inside the period?
+      if (!s.every && (st.o.status == cronwalk::kStUnschedulable || (st.o.next != kZero && st.o.next >= nhi))) {
+        defer = true;
+      } else if (!s.every) {
+        if (st.o.last != kZero) st.o.last -= shift;
+        if (st.o.next != kZero) st.o.next -= shift;
+      }
+    }
+    if (rejected) *rejected = defer;
   } else if (kMode == kUnmetEasy) {
 #pragma unroll 1
     for (int round = 0; round < kUnmetEasyRounds; ++round) {

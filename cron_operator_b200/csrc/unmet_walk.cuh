@@ -98,6 +98,20 @@ CW_HD void chain_fast_forward(const Spec& s, Walk& w, int64_t limit, uint32_t* m
   if (!(((s.month >> w.M) & 1u) && day_matches(s, w.D, w.dn) && ((s.hour >> w.hour()) & 1u) &&
         ((s.minute >> w.minute()) & 1ULL) && ((s.second >> w.second()) & 1ULL)))
     return;
+#if B200CRON_ZONED_TIER0
+  if (!kUtcOnly && w.zn > 1 && limit < w.pe && w.natural(w.t + w.off) && w.natural(limit + w.off)) {
+    // Tier 0 (see fast_next): the whole stretch up to `limit` lies in the natural window of the current period, where
+    // every condition below holds trivially -- count on the local clock with the UTC instantiation.
+    Walk u = w;
+    u.t = w.t + w.off;
+    u.off = 0;  // the local clock, read as UTC
+    chain_fast_forward<true>(s, u, limit + w.off, missed);
+    w.t = u.t - w.off;
+    w.dn = u.dn; w.sod = u.sod; w.Y = u.Y; w.M = u.M; w.D = u.D;
+    w.today_ok = u.today_ok; w.dm_ok = u.dm_ok;
+    return;
+  }
+#endif
   // ---- (1) rest of the current local day, up to the period edge ----
   const int64_t day_end = w.t + (86400 - w.sod);  // absolute instant of the next local midnight at this offset
   {
