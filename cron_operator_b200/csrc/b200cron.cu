@@ -252,7 +252,7 @@ cudaError_t launch_unmet(b200cron_ctx* ctx, Device& d, cudaStream_t st, const Un
   const unsigned tiles = (unsigned)((a.n + kUnmetTile - 1) / kUnmetTile);
   if (!a.zone_id) {  // every Cron in UTC: the closed form always answers, nothing can be deferred, no scratch
     ctx->launches.fetch_add(1, std::memory_order_relaxed);
-    unmet_tile_kernel<false><<<tiles, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, nullptr, nullptr);
+    unmet_tile_kernel<false><<<tiles, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, nullptr, nullptr, nullptr, nullptr);
     return cudaGetLastError();
   }
   DeferList& b = d.defer[d.defer_next];
@@ -262,13 +262,14 @@ cudaError_t launch_unmet(b200cron_ctx* ctx, Device& d, cudaStream_t st, const Un
   const int32_t nz = d.zt.nzones;
   if (!b.done) {
     if ((e = cudaEventCreateWithFlags(&b.done, cudaEventDisableTiming)) != cudaSuccess) return e;
-    // counters: [0] defer count | [1 .. nz] zone histogram | [nz+1 .. 2nz+1] cursors, the last one = ordered-list length
-    if ((e = cudaMalloc(&b.count, (2 * (size_t)nz + 2) * sizeof(uint32_t))) != cudaSuccess) return e;
+    // counters: [0] defer count | [1] class-B count | [2 .. nz+1] zone histogram | [nz+2 .. 2nz+2] cursors (last = total)
+    if ((e = cudaMalloc(&b.count, (2 * (size_t)nz + 3) * sizeof(uint32_t))) != cudaSuccess) return e;
   } else if ((e = cudaStreamWaitEvent(st, b.done, 0)) != cudaSuccess) {
     return e;
   }
   const bool ordered = B200CRON_UNMET_PLAN == 1;
-  const size_t need = ordered ? 2 * a.n : a.n;  // defer list (every Cron may be deferred) [+ zone-ordered list]
+  // defer list (every Cron may be deferred) [+ class-B list + zone-ordered list]
+  const size_t need = ordered ? 3 * a.n : a.n;
   if (need > b.cap) {
     if (b.idx) {
       if ((e = cudaEventSynchronize(b.done)) != cudaSuccess) return e;
@@ -281,23 +282,25 @@ cudaError_t launch_unmet(b200cron_ctx* ctx, Device& d, cudaStream_t st, const Un
   }
   const unsigned grid = (unsigned)((a.n + kUnmetThreads - 1) / kUnmetThreads);
   if (ordered) {
-    uint32_t* hist = b.count + 1;
+    uint32_t* z1_count = b.count + 1;
+    uint32_t* hist = b.count + 2;
     uint32_t* cursor = hist + nz;
-    uint32_t* order = b.idx + a.n;
-    if ((e = cudaMemsetAsync(b.count, 0, (size_t)(nz + 1) * sizeof(uint32_t), st)) != cudaSuccess) return e;
+    uint32_t* z1_list = b.idx + a.n;
+    uint32_t* order = b.idx + 2 * a.n;
+    if ((e = cudaMemsetAsync(b.count, 0, (size_t)(nz + 2) * sizeof(uint32_t), st)) != cudaSuccess) return e;
     const unsigned zgrid = (unsigned)((a.n + kZoneOrderTile - 1) / kZoneOrderTile);
     ctx->launches.fetch_add(6, std::memory_order_relaxed);
-    zone_order_hist_kernel<<<zgrid, kZoneOrderThreads, (size_t)nz * sizeof(uint32_t), st>>>(a.zone_id, a.n, nz, hist);
+    unmet_tile_kernel<false><<<tiles, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, nullptr, nullptr, z1_list, z1_count);
+    zone_order_hist_kernel<<<zgrid, kZoneOrderThreads, (size_t)nz * sizeof(uint32_t), st>>>(a.zone_id, z1_list, z1_count, nz, hist);
     zone_order_scan_kernel<<<1, kZoneOrderThreads, 0, st>>>(hist, nz, cursor);
-    zone_order_scatter_kernel<<<zgrid, kZoneOrderThreads, 2 * (size_t)nz * sizeof(uint32_t), st>>>(a.zone_id, a.n, nz,
-                                                                                                  cursor, order);
-    unmet_tile_kernel<false><<<tiles, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, nullptr, nullptr);
+    zone_order_scatter_kernel<<<zgrid, kZoneOrderThreads, 2 * (size_t)nz * sizeof(uint32_t), st>>>(a.zone_id, z1_list, z1_count,
+                                                                                                  nz, cursor, order);
     // the scatter advanced cursor[z] to the end of zone z's range; cursor[nz] (the total) is untouched
     unmet_ordered_kernel<<<grid, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, b.idx, b.count, order, cursor + nz);
   } else {
     if ((e = cudaMemsetAsync(b.count, 0, sizeof(uint32_t), st)) != cudaSuccess) return e;
     ctx->launches.fetch_add(2, std::memory_order_relaxed);
-    unmet_tile_kernel<true><<<tiles, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, b.idx, b.count);
+    unmet_tile_kernel<true><<<tiles, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, b.idx, b.count, nullptr, nullptr);
   }
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
   const unsigned hard_max = (unsigned)d.sm_count * B200CRON_UNMET_HARD_MINBLOCKS;

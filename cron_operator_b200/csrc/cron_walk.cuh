@@ -29,9 +29,6 @@
 #define CW_LDG(p) (*(p))
 #endif
 
-#ifndef B200CRON_ZONED_TIER0
-#define B200CRON_ZONED_TIER0 1  // zoned calls far from a transition take the UTC closed form on the local clock (fast_next)
-#endif
 #ifndef CW_TRACE
 #define CW_TRACE(tag, w)
 #endif
@@ -630,29 +627,6 @@ CW_HD bool fast_next(const Spec& s, Walk& w, int64_t* out) {
   // natural() is trivially true for UTC (one infinite period, offset 0), so all lanes run the same code.
   const bool prereq = kUtcOnly || ((w.off % 60 == 0) && w.natural((int64_t)w.dn * 86400 + (sod / 3600) * 3600));  // hour reset Date(Y,M,D,h,0,0)
   if (!prereq) return false;
-#if B200CRON_ZONED_TIER0
-  if (zoned) {
-    // Tier 0: most zoned calls never come near a transition.  Inside one period local time is UTC shifted by the
-    // offset, so run the UTC closed form on the local clock and accept its answer when the whole search lies in the
-    // natural window of the current period: from the earliest Date() target upstream can make -- the midnight of t's
-    // day (day reset) or of the 1st of t's month (month reset), both BEFORE t -- to the fire.  Every Date() target and
-    // every Add-based stretch of upstream's walk then sits inside this period.  Anything else (a fire beyond the
-    // period, a reset target before it, no fire within five years) is left to the general code below, `w` untouched.
-    Walk u = w;
-    u.t = w.t + w.off;
-    u.off = 0;  // the local clock, read as UTC
-    int64_t r = kZero;
-    fast_next<true>(s, u, &r);
-    const int64_t x_lo = (int64_t)(((s.month >> w.M) & 1u) ? w.dn : w.dn - (w.D - 1)) * 86400;
-    if (r != kZero && r < w.nhi && x_lo >= w.nlo) {
-      w.t = r - w.off;
-      w.dn = u.dn; w.sod = u.sod; w.Y = u.Y; w.M = u.M; w.D = u.D;
-      w.today_ok = u.today_ok; w.dm_month = u.dm_month; w.dm_ok = u.dm_ok;
-      *out = w.t;
-      return true;
-    }
-  }
-#endif
   // Chained-call shortcut: the previous fire was the last of its (matching) day, the resident month's day mask is
   // cached, and the next matching day lies in the same month.  Upstream wraps at the next local midnight
   // (Add-based, must happen inside this period), crosses the non-matching days with AddDate steps at hour 0 (all

@@ -517,11 +517,7 @@ __device__ __forceinline__ void unmet_one(const UnmetArgs& a, const ZoneTable& z
     if (s.every) {
       st.o = cronwalk::unmet_decide_every((int64_t)s.second, in);  // "@every <dur>": closed form, no walk
     } else if (kMode == kUnmetUtc) {
-      st.o.decision = cronwalk::unmet_gate(in);  // the gates look at the real clock
-      if (st.o.decision == 0) {
-        in.earliest += shift; in.now += shift; in.deadline = kZero; in.flags = 0;
-        cronwalk::unmet_begin(zt, 0, in, st);
-      }
+      cronwalk::unmet_begin_shifted(zt, in, shift, st);
     } else {
       cronwalk::unmet_begin(zt, zone, in, st);
     }
@@ -532,14 +528,7 @@ __device__ __forceinline__ void unmet_one(const UnmetArgs& a, const ZoneTable& z
     while (__any_sync(0xffffffffu, !st.done)) {
       if (!st.done) cronwalk::unmet_step_utc(s, in, st);
     }
-    if (shift != 0 || nhi != cronwalk::kOmega) {  // a zoned lane: did every call stay inside the period?
-      if (!s.every && (st.o.status == cronwalk::kStUnschedulable || (st.o.next != kZero && st.o.next >= nhi))) {
-        defer = true;
-      } else if (!s.every) {
-        if (st.o.last != kZero) st.o.last -= shift;
-        if (st.o.next != kZero) st.o.next -= shift;
-      }
-    }
+    if (ok && !s.every) defer = cronwalk::unmet_finish_shifted(shift, nhi, st);  // did every call stay in the period?
     if (rejected) *rejected = defer;
   } else if (kMode == kUnmetEasy) {
 #pragma unroll 1
@@ -580,52 +569,90 @@ unmet_single_kernel(UnmetArgs a, ZoneTable zt, int* __restrict__ err) {
   unmet_one<kUnmetSingle>(a, zt, err, q, q < a.n, nullptr, nullptr);
 }
 
-// Input-order tiles with class-pure warps (see above).  kZoned: the zoned class is also handled here (easy rounds);
-// otherwise only the UTC class is, and the zoned Crons are left to unmet_ordered_kernel.  A launch without zone ids
-// is all UTC: no classification, no defer list.
-constexpr int kUnmetTile = 512;  // Crons per CTA: ~8 warps' worth per class on a half-UTC workload
+// Input-order tiles with class-pure warps (see above).  Class A = Crons the UTC machine can answer: evaluated in UTC,
+// or in a zone whose single period [ps, pe) holds the Cron's whole window -- from 32 days before min(earliest, now)
+// (which covers every Date() reset target: the midnight of the day or of the 1st of the month) to now; the machine then
+// runs on that period's local clock (unmet_one's `shift`) and a lane whose Next() leaves the period is rejected into
+// class B.  Class B = the zoned Crons with a transition in their window: kZoned handles them here (easy rounds);
+// otherwise they are appended to `z1_list` for the zone-ordered kernel.  A launch without zone ids is all class A: no
+// classification, no lists.
+constexpr int kUnmetTile = 512;  // Crons per CTA: ~12 + 4 warps' worth on a half-UTC workload
 template <bool kZoned>
 __global__ void __launch_bounds__(kUnmetThreads, B200CRON_UNMET_EASY_MINBLOCKS)
 unmet_tile_kernel(UnmetArgs a, ZoneTable zt, int* __restrict__ err, uint32_t* __restrict__ defer_idx,
-                  uint32_t* __restrict__ defer_count) {
+                  uint32_t* __restrict__ defer_count, uint32_t* __restrict__ z1_list, uint32_t* __restrict__ z1_count) {
   const size_t base = (size_t)blockIdx.x * kUnmetTile;
   const int cnt = (int)((a.n - base) < (size_t)kUnmetTile ? (a.n - base) : (size_t)kUnmetTile);
-  // deal the tile's Crons into the two classes: UTC indices packed from the front of s_idx, zoned ones from the back
-  // (a launch without zone ids is all UTC: identity order, no classification)
+  // class A indices packed from the front of s_idx, class B from the back; a class-A entry keeps its clock shift and
+  // the end of its period's natural window on the local clock (zone-less launch: identity order, no shift)
   __shared__ uint16_t s_idx[kUnmetTile];
-  __shared__ int s_n[2];
-  if (threadIdx.x < 2) s_n[threadIdx.x] = threadIdx.x == 0 && a.zone_id == nullptr ? cnt : 0;
+  __shared__ int32_t s_shift[kUnmetTile];
+  __shared__ int64_t s_nhi[kUnmetTile];
+  __shared__ uint16_t s_rej[kUnmetTile];  // class-A entries whose Next() left their period: they join class B
+  __shared__ int s_n[3];
+  if (threadIdx.x < 3) s_n[threadIdx.x] = threadIdx.x == 0 && a.zone_id == nullptr ? cnt : 0;
   __syncthreads();
   const unsigned lane = threadIdx.x & 31u;
-#pragma unroll
+  const unsigned below = (1u << lane) - 1u;
+#pragma unroll 1
   for (int it = 0; it < kUnmetTile / kUnmetThreads; ++it) {
     if (a.zone_id == nullptr) break;
     const int q = it * kUnmetThreads + threadIdx.x;
     const bool in = q < cnt;
-    const bool zoned = in && __ldg(a.zone_id + base + q) != 0;
-    const unsigned mz = __ballot_sync(0xffffffffu, zoned), mu = __ballot_sync(0xffffffffu, in && !zoned);
-    int bu = 0, bz = 0;
-    if (lane == 0) {
-      if (mu) bu = atomicAdd(&s_n[0], __popc(mu));
-      if (mz) bz = atomicAdd(&s_n[1], __popc(mz));
+    int32_t shift = 0;
+    int64_t nhi = cronwalk::kOmega;
+    bool cls_b = false;
+    if (in) {
+      const int32_t z = __ldg(a.zone_id + base + q);
+      // invalid ids are class B too: the general path reports them
+      if (z != 0) cls_b = !cronwalk::unmet_class_a(zt, z, __ldg(a.earliest + base + q), a.now, kMinTime, kMaxTime,
+                                                   zt.horizon - kSixYears, &shift, &nhi);
     }
-    bu = __shfl_sync(0xffffffffu, bu, 0);
-    bz = __shfl_sync(0xffffffffu, bz, 0);
-    const unsigned below = (1u << lane) - 1u;
-    if (in && !zoned) s_idx[bu + __popc(mu & below)] = (uint16_t)q;
-    if (zoned) s_idx[kUnmetTile - 1 - (bz + __popc(mz & below))] = (uint16_t)q;
+    const unsigned mb = __ballot_sync(0xffffffffu, cls_b), ma = __ballot_sync(0xffffffffu, in && !cls_b);
+    int ba = 0, bb = 0;
+    if (lane == 0) {
+      if (ma) ba = atomicAdd(&s_n[0], __popc(ma));
+      if (mb) bb = atomicAdd(&s_n[1], __popc(mb));
+    }
+    ba = __shfl_sync(0xffffffffu, ba, 0);
+    bb = __shfl_sync(0xffffffffu, bb, 0);
+    if (in && !cls_b) {
+      const int slot = ba + __popc(ma & below);
+      s_idx[slot] = (uint16_t)q; s_shift[slot] = shift; s_nhi[slot] = nhi;
+    }
+    if (cls_b) s_idx[kUnmetTile - 1 - (bb + __popc(mb & below))] = (uint16_t)q;
   }
   __syncthreads();
-  const int nu = s_n[0], nz = s_n[1];
-  for (int q = threadIdx.x; q < ((nu + 31) & ~31); q += kUnmetThreads) {
-    const bool live = q < nu;
-    unmet_one<kUnmetUtc>(a, zt, err, base + (live ? (a.zone_id ? (int)s_idx[q] : q) : 0), live, nullptr, nullptr);
-  }
-  if (kZoned) {
-    for (int q = threadIdx.x; q < ((nz + 31) & ~31); q += kUnmetThreads) {
-      const bool live = q < nz;
-      unmet_one<kUnmetEasy>(a, zt, err, base + (live ? s_idx[kUnmetTile - 1 - q] : 0), live, defer_idx, defer_count);
+  const int na = s_n[0];
+  for (int q = threadIdx.x; q < ((na + 31) & ~31); q += kUnmetThreads) {
+    const bool live = q < na;
+    const bool plain = a.zone_id == nullptr;
+    const int li = live ? (plain ? q : (int)s_idx[q]) : 0;
+    bool rejected = false;
+    unmet_one<kUnmetUtc>(a, zt, err, base + li, live, nullptr, nullptr, (live && !plain) ? s_shift[q] : 0,
+                         (live && !plain) ? s_nhi[q] : cronwalk::kOmega, &rejected);
+    const unsigned mr = __ballot_sync(0xffffffffu, rejected);
+    if (mr) {
+      int br = 0;
+      if (lane == 0) br = atomicAdd(&s_n[2], __popc(mr));
+      br = __shfl_sync(0xffffffffu, br, 0);
+      if (rejected) s_rej[br + __popc(mr & below)] = (uint16_t)li;
     }
+  }
+  if (a.zone_id == nullptr) return;
+  __syncthreads();
+  const int nb = s_n[1], nr = s_n[2];
+  auto class_b = [&](int q) { return q < nb ? s_idx[kUnmetTile - 1 - q] : s_rej[q - nb]; };
+  if (kZoned) {
+    for (int q = threadIdx.x; q < ((nb + nr + 31) & ~31); q += kUnmetThreads) {
+      const bool live = q < nb + nr;
+      unmet_one<kUnmetEasy>(a, zt, err, base + (live ? class_b(q) : 0), live, defer_idx, defer_count);
+    }
+  } else if (nb + nr > 0) {
+    __shared__ uint32_t s_base;
+    if (threadIdx.x == 0) s_base = atomicAdd(z1_count, (uint32_t)(nb + nr));
+    __syncthreads();
+    for (int q = threadIdx.x; q < nb + nr; q += kUnmetThreads) z1_list[s_base + q] = (uint32_t)(base + class_b(q));
   }
 }
 
@@ -656,40 +683,41 @@ unmet_hard_kernel(UnmetArgs a, ZoneTable zt, int* __restrict__ err, const uint32
 }
 
 // -------------------------------------------------------------------------------------------------------------
-// Zone order: a counting sort of the ZONED Crons' indices by zone id (histogram, scan, scatter; one pass over zone_id
-// each).  Crons evaluated in UTC (zone id 0) are left out -- the tile kernel handles them in place; ids outside
-// [0, nzones) are binned with zone 1 and reported by unmet_one as before.  cursor[nzones] receives the list's length.
+// Zone order: a counting sort by zone id of the Crons in `list` (the class-B Crons unmet_tile_kernel collected; its
+// length *count is known only on the device, so the grids cover n and CTAs past the end leave at once): histogram,
+// scan, scatter -- one pass over the list each.  Ids outside [0, nzones) are binned with zone 1 and reported by
+// unmet_one as before.  cursor[nzones] receives the list's length.
 // -------------------------------------------------------------------------------------------------------------
 constexpr int kZoneOrderThreads = 256;
-constexpr int kZoneOrderItems = 16;  // Crons per thread: a CTA bins 4096 consecutive Crons
+constexpr int kZoneOrderItems = 16;  // Crons per thread: a CTA bins 4096 consecutive list entries
 constexpr int kZoneOrderTile = kZoneOrderThreads * kZoneOrderItems;
 
-__device__ __forceinline__ uint32_t zone_bin(const int32_t* __restrict__ zone_id, size_t i, int32_t nzones) {
+__device__ __forceinline__ uint32_t zone_bin(const int32_t* __restrict__ zone_id, uint32_t i, int32_t nzones) {
   const int32_t z = __ldg(zone_id + i);
-  return (z < 0 || z >= nzones) ? 1u : (uint32_t)z;
+  return (z <= 0 || z >= nzones) ? 1u : (uint32_t)z;
 }
 
-// the CTA's histogram of its tile in shared memory (bins [0, nzones)); all threads call it
-__device__ __forceinline__ void zone_tile_hist(const int32_t* __restrict__ zone_id, size_t n, int32_t nzones,
-                                               uint32_t* __restrict__ sh) {
+// the CTA's histogram of its tile of the list in shared memory (bins [0, nzones)); all threads call it
+__device__ __forceinline__ void zone_tile_hist(const int32_t* __restrict__ zone_id, const uint32_t* __restrict__ list,
+                                               uint32_t count, int32_t nzones, uint32_t* __restrict__ sh) {
   for (int b = threadIdx.x; b < nzones; b += kZoneOrderThreads) sh[b] = 0;
   __syncthreads();
   const size_t base = (size_t)blockIdx.x * kZoneOrderTile;
 #pragma unroll 4
   for (int it = 0; it < kZoneOrderItems; ++it) {
-    const size_t i = base + (size_t)it * kZoneOrderThreads + threadIdx.x;
-    if (i < n) {
-      const uint32_t b = zone_bin(zone_id, i, nzones);
-      if (b) atomicAdd(&sh[b], 1u);
-    }
+    const size_t q = base + (size_t)it * kZoneOrderThreads + threadIdx.x;
+    if (q < count) atomicAdd(&sh[zone_bin(zone_id, __ldg(list + q), nzones)], 1u);
   }
   __syncthreads();
 }
 
 __global__ void __launch_bounds__(kZoneOrderThreads)
-zone_order_hist_kernel(const int32_t* __restrict__ zone_id, size_t n, int32_t nzones, uint32_t* __restrict__ hist) {
+zone_order_hist_kernel(const int32_t* __restrict__ zone_id, const uint32_t* __restrict__ list,
+                       const uint32_t* __restrict__ count, int32_t nzones, uint32_t* __restrict__ hist) {
   extern __shared__ uint32_t zo_sh[];
-  zone_tile_hist(zone_id, n, nzones, zo_sh);
+  const uint32_t cnt = __ldg(count);
+  if ((size_t)blockIdx.x * kZoneOrderTile >= cnt) return;
+  zone_tile_hist(zone_id, list, cnt, nzones, zo_sh);
   for (int b = threadIdx.x; b < nzones; b += kZoneOrderThreads)
     if (zo_sh[b]) atomicAdd(hist + b, zo_sh[b]);
 }
@@ -717,11 +745,14 @@ zone_order_scan_kernel(const uint32_t* __restrict__ hist, int32_t nzones, uint32
 
 // every CTA reserves, per zone, a range of the output for its tile's Crons and fills it
 __global__ void __launch_bounds__(kZoneOrderThreads)
-zone_order_scatter_kernel(const int32_t* __restrict__ zone_id, size_t n, int32_t nzones, uint32_t* __restrict__ cursor,
+zone_order_scatter_kernel(const int32_t* __restrict__ zone_id, const uint32_t* __restrict__ list,
+                          const uint32_t* __restrict__ count, int32_t nzones, uint32_t* __restrict__ cursor,
                           uint32_t* __restrict__ order) {
   extern __shared__ uint32_t zo_sh[];  // [nzones] counts, then local cursors; [nzones] bases
   uint32_t* sh_base = zo_sh + nzones;
-  zone_tile_hist(zone_id, n, nzones, zo_sh);
+  const uint32_t cnt = __ldg(count);
+  if ((size_t)blockIdx.x * kZoneOrderTile >= cnt) return;
+  zone_tile_hist(zone_id, list, cnt, nzones, zo_sh);
   for (int b = threadIdx.x; b < nzones; b += kZoneOrderThreads) {
     const uint32_t c = zo_sh[b];
     sh_base[b] = c ? atomicAdd(cursor + b, c) : 0u;
@@ -731,10 +762,11 @@ zone_order_scatter_kernel(const int32_t* __restrict__ zone_id, size_t n, int32_t
   const size_t base = (size_t)blockIdx.x * kZoneOrderTile;
 #pragma unroll 4
   for (int it = 0; it < kZoneOrderItems; ++it) {
-    const size_t i = base + (size_t)it * kZoneOrderThreads + threadIdx.x;
-    if (i < n) {
+    const size_t q = base + (size_t)it * kZoneOrderThreads + threadIdx.x;
+    if (q < cnt) {
+      const uint32_t i = __ldg(list + q);
       const uint32_t b = zone_bin(zone_id, i, nzones);
-      if (b) order[sh_base[b] + atomicAdd(&zo_sh[b], 1u)] = (uint32_t)i;
+      order[sh_base[b] + atomicAdd(&zo_sh[b], 1u)] = i;
     }
   }
 }

@@ -98,20 +98,6 @@ CW_HD void chain_fast_forward(const Spec& s, Walk& w, int64_t limit, uint32_t* m
   if (!(((s.month >> w.M) & 1u) && day_matches(s, w.D, w.dn) && ((s.hour >> w.hour()) & 1u) &&
         ((s.minute >> w.minute()) & 1ULL) && ((s.second >> w.second()) & 1ULL)))
     return;
-#if B200CRON_ZONED_TIER0
-  if (!kUtcOnly && w.zn > 1 && limit < w.pe && w.natural(w.t + w.off) && w.natural(limit + w.off)) {
-    // Tier 0 (see fast_next): the whole stretch up to `limit` lies in the natural window of the current period, where
-    // every condition below holds trivially -- count on the local clock with the UTC instantiation.
-    Walk u = w;
-    u.t = w.t + w.off;
-    u.off = 0;  // the local clock, read as UTC
-    chain_fast_forward<true>(s, u, limit + w.off, missed);
-    w.t = u.t - w.off;
-    w.dn = u.dn; w.sod = u.sod; w.Y = u.Y; w.M = u.M; w.D = u.D;
-    w.today_ok = u.today_ok; w.dm_ok = u.dm_ok;
-    return;
-  }
-#endif
   // ---- (1) rest of the current local day, up to the period edge ----
   const int64_t day_end = w.t + (86400 - w.sod);  // absolute instant of the next local midnight at this offset
   {
@@ -377,6 +363,70 @@ CW_HD void unmet_step_utc(const Spec& s, const UnmetIn& in, UnmetState& st) {
   st.o.last = st.w.t;
   st.arg = st.w.t;
   st.resident = true;
+}
+
+// ---- the UTC machine on one zone period's local clock -----------------------------------------------------------
+// Inside one constant-offset period local time is UTC moved by the offset.  When a Cron's whole window lies inside
+// the natural window of ONE period -- from the earliest Date() target upstream can make (the midnight of the 1st of
+// earliest's month at the latest 32 days back) to the last Next() result -- every Date() resolves naturally and every
+// Add-based stretch stays in the period, so upstream's walk is the UTC walk on that clock.
+//
+// unmet_class_a: does the period in force 32 days before min(earliest, now) still hold now?  (t_min / t_max: supported
+// absolute range; zoned_max: zoned evaluations must start below it.)  *shift = the period's offset, *nhi = end of its
+// natural window on the local clock.  Invalid ids and anything doubtful say no: the general path decides and reports.
+CW_HD bool unmet_class_a(const ZoneTable& zt, int32_t zone, int64_t earliest, int64_t now, int64_t t_min, int64_t t_max,
+                         int64_t zoned_max, int32_t* shift, int64_t* nhi) {
+  if (zone <= 0 || zone >= zt.nzones) return false;
+  const int64_t lo = earliest < now ? earliest : now;
+  if (lo < t_min + 33 * 86400LL || now > t_max) return false;
+  Walk w;
+  w.bind_zone(zt, zone);
+  if (w.zn > 1 && now >= zoned_max) return false;
+  const int32_t off = w.lookup(lo - 32 * 86400LL);
+  if (!(now < w.pe) || off % 60 != 0) return false;
+  *shift = off;
+  *nhi = w.nhi;
+  return true;
+}
+// gates on the real clock, then `in` moves onto the local clock and the UTC machine starts
+CW_HD void unmet_begin_shifted(const ZoneTable& zt, UnmetIn& in, int32_t shift, UnmetState& st) {
+  st.o.last = kZero; st.o.next = kZero; st.o.missed = 0; st.o.status = kStOk;
+  st.done = true;
+  st.w.bind_utc();
+  st.o.decision = unmet_gate(in);
+  if (st.o.decision) return;
+  in.earliest += shift; in.now += shift; in.deadline = kZero; in.flags = 0;
+  unmet_begin(zt, 0, in, st);
+}
+// after the machine has run: true = some Next() left the period (or found nothing in five years, i.e. searched beyond
+// it) and the answer must come from the general path; false = st.o holds the answer, moved back to the real clock
+CW_HD bool unmet_finish_shifted(int32_t shift, int64_t nhi, UnmetState& st) {
+  if (shift == 0 && nhi == kOmega) return false;  // a Cron evaluated in UTC: one endless period
+  if (st.o.status == kStUnschedulable || (st.o.next != kZero && st.o.next >= nhi)) return true;
+  if (st.o.last != kZero) st.o.last -= shift;
+  if (st.o.next != kZero) st.o.next -= shift;
+  return false;
+}
+
+// the kernels' class logic in one place (host build / tests): UTC machine for class A, general machine otherwise
+CW_HD UnmetOut unmet_decide_classed(const Spec& s, const ZoneTable& zt, int32_t zone, const UnmetIn& in0, int64_t t_min,
+                                    int64_t t_max, int64_t zoned_max, int* klass) {
+  int32_t shift = 0;
+  int64_t nhi = kOmega;
+  *klass = 2;
+  if (!s.every && (zone == 0 || unmet_class_a(zt, zone, in0.earliest, in0.now, t_min, t_max, zoned_max, &shift, &nhi))) {
+    UnmetIn in = in0;
+    UnmetState st;
+    unmet_begin_shifted(zt, in, shift, st);
+    while (!st.done) unmet_step_utc(s, in, st);
+    if (!unmet_finish_shifted(shift, nhi, st)) { *klass = zone == 0 ? 0 : 1; return st.o; }
+    *klass = 3;  // rejected: joins class B
+  }
+  if (s.every) return unmet_decide_every((int64_t)s.second, in0);
+  UnmetState st;
+  unmet_begin(zt, zone, in0, st);
+  while (!st.done) unmet_step(s, in0, st);
+  return st.o;
 }
 
 CW_HD UnmetOut unmet_decide_utc(const Spec& s, const ZoneTable& zt, const UnmetIn& in) {

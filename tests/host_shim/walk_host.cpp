@@ -72,6 +72,9 @@ void shim_next_n(void* table, const uint64_t* const masks[6], const int32_t* zon
   }
 }
 
+static uint8_t* g_klass = nullptr;  // optional: which class answered each Cron of the next shim_unmet call
+void shim_set_klass_out(uint8_t* p) { g_klass = p; }
+
 void shim_unmet(void* table, const uint64_t* const masks[6], const int32_t* zone_id, const int64_t* earliest,
                 int64_t now, int32_t now_nsec, const uint8_t* policy, const uint32_t* active, const uint8_t* flags,
                 const int64_t* deadline, size_t n, int64_t* last, int64_t* next, uint32_t* missed, uint8_t* status,
@@ -87,9 +90,12 @@ void shim_unmet(void* table, const uint64_t* const masks[6], const int32_t* zone
     in.active = active ? active[i] : 0;
     in.flags = flags ? flags[i] : 0;
     in.deadline = deadline ? deadline[i] : kZero;
-    // as the kernels do: Crons evaluated in UTC (no zone ids, or id 0) take the UTC machine, the rest the general one
+    // as the kernels do: class A (UTC, or one zone period holding the whole window) takes the UTC machine on that
+    // period's clock, everything else -- and what that machine rejects -- the general one
     const int32_t z = zone_id ? zone_id[i] : 0;
-    UnmetOut o = s.every ? unmet_decide_every((int64_t)s.second, in) : z == 0 ? unmet_decide_utc(s, zt, in) : unmet_decide(s, zt, z, in);
+    int klass = 0;
+    UnmetOut o = unmet_decide_classed(s, zt, z, in, -62135596800LL, 253402300799LL, zt.horizon - 6LL * 366 * 86400, &klass);
+    if (g_klass) g_klass[i] = (uint8_t)klass;
     last[i] = o.last; next[i] = o.next; missed[i] = o.missed; status[i] = o.status; decision[i] = o.decision;
   }
 }

@@ -39,6 +39,7 @@ def lib():
         L.shim_unmet.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p,
                                  C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p,
                                  C.c_void_p, C.c_void_p]
+        L.shim_set_klass_out.argtypes = [C.c_void_p]
         L.shim_unmet_two_phase.argtypes = ([C.c_void_p] * 4 + [C.c_int64, C.c_int32] + [C.c_void_p] * 4 +
                                            [C.c_size_t, C.c_int] + [C.c_void_p] * 7)
         _LIB = L
@@ -87,9 +88,13 @@ def next_n(masks, from_, k=1, zone_id=None, t=None):
     return out
 
 
-def unmet(masks, earliest, now, now_nsec=0, policy=None, active=None, flags=None, deadline=None, zone_id=None, t=None):
+def unmet(masks, earliest, now, now_nsec=0, policy=None, active=None, flags=None, deadline=None, zone_id=None, t=None,
+          klass_out=None):
+    """klass_out (uint8 array): receives which path answered each Cron -- 0 UTC machine, 1 UTC machine on a zone
+    period's clock, 2 general machine, 3 general machine after the period machine rejected the Cron"""
     t = t or table()
     n = masks.shape[1]
+    lib().shim_set_klass_out(None if klass_out is None else klass_out.ctypes.data)
     earliest = np.ascontiguousarray(earliest, dtype=np.int64)
     cv = lambda a, dt: None if a is None else np.ascontiguousarray(a, dtype=dt)  # noqa: E731
     zid, policy, active = cv(zone_id, np.int32), cv(policy, np.uint8), cv(active, np.uint32)

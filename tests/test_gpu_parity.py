@@ -775,3 +775,32 @@ def test_history_chunking_wide_keys_and_length_limit(ctx):
     assert np.array_equal(p[3:3 + 65_537], np.arange(65_537)) and bool((keep[3:3 + 65_537] == 1).all())  # left as is
     w0, _ = po.history_prune(key[:3], None)
     assert np.array_equal(p[:3].view(np.uint32), w0)                                                     # neighbours fine
+
+
+def test_unmet_period_clock_class_on_the_device(ctx, names):
+    """the unmet kernels answer a zoned Cron whose whole window lies in one zone period with the UTC machine on that
+    period's clock, and hand it to the general path when a Next() leaves the period (tests/test_unmet_host.py has the
+    host-side twin): mixed zones, windows ending around transitions, sparse specs with a far next fire"""
+    rng = np.random.default_rng(77)
+    zones = ["Asia/Tokyo", "Asia/Kolkata", "Asia/Kathmandu", "Europe/Berlin", "America/New_York", "Australia/Sydney",
+             "America/Santiago", "Pacific/Chatham", "Africa/Cairo", "Atlantic/Azores", "Asia/Tehran", "America/Sao_Paulo",
+             "Australia/Lord_Howe", "UTC", "Etc/GMT+12", "Pacific/Apia"]
+    n = 60_001
+    masks = synth.gen_specs(n, seed=78, dense_minutes=0.3)
+    zid = np.array([names.index(z) for z in zones], np.int32)[rng.integers(0, len(zones), n)]
+    for now in (ts(2026, 3, 29, 12), ts(2026, 7, 15, 3, 7, 9), ts(2026, 10, 25, 0, 59, 59), ts(2027, 1, 1)):
+        earliest = now - synth.gen_times(n, -7200, 20 * 86400, seed=int(now % 1000))
+        got = ctx.unmet_since(masks, earliest, now, zone_id=zid)
+        _cmp(got, po.batch_unmet(masks, earliest, now, zone_id=zid, zone_names=names), now)
+    z = names.index("Europe/Berlin")
+    when = ctx.zone_periods(z)[0]
+    texts = ["* * * * *", "*/5 * * * *", "30 2 * * *", "0 0 * * *", "0 0 1 * *", "15 3 * * 0", "59 23 31 12 *", "0 12 1 1 *"]
+    base = _masks_of(texts)
+    S = len(texts)
+    for t in [int(w) for w in when if ts(2025) < w < ts(2027)]:
+        for back, ahead in [(40 * 86400, -33 * 86400), (40 * 86400, -1), (86400, -1), (3600, 3600), (10, 40 * 86400), (0, 86400)]:
+            zz = np.full(S, z, np.int32)
+            e, now = np.full(S, t - back), t + ahead
+            if now < t - back:
+                continue
+            _cmp(ctx.unmet_since(base, e, now, zone_id=zz), po.batch_unmet(base, e, now, zone_id=zz, zone_names=names), (t, back, ahead))

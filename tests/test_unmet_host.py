@@ -287,3 +287,39 @@ def test_every_schedules_in_mixed_batches():
     for text, d in (("@every 90s", 90), ("@every 1h30m", 5400), ("@every 500ms", 1), ("TZ=Asia/Tokyo @every 2h", 7200)):
         s, kind, every, _ = po.parse_standard(text)
         assert (kind, every) == (1, d) and s.tuple() == (0, 0, 0, d, 1 << 62, 0)
+
+
+def test_period_clock_machine_matches_literal_chain():
+    """class A of the unmet kernels: a zoned Cron whose whole window lies in one zone period is answered by the UTC
+    machine on that period's local clock, and rejected into the general machine when a Next() leaves the period; both
+    must give the literal chain's answers.  Mixed zones (fixed-offset, 30/45-minute, DST on both hemispheres), windows
+    that end days, hours or seconds before / after a transition, sparse specs whose next fire is months away."""
+    rng = np.random.default_rng(77)
+    zones = ["Asia/Tokyo", "Asia/Kolkata", "Asia/Kathmandu", "Europe/Berlin", "America/New_York", "Australia/Sydney",
+             "America/Santiago", "Pacific/Chatham", "Africa/Cairo", "Atlantic/Azores", "Asia/Tehran", "America/Sao_Paulo",
+             "Australia/Lord_Howe", "UTC", "Etc/GMT+12", "Pacific/Apia"]
+    n = 40_000
+    masks = synth.gen_specs(n, seed=78, dense_minutes=0.3)
+    zid = np.array([NAMES.index(z) for z in zones], np.int32)[rng.integers(0, len(zones), n)]
+    klass = np.zeros(n, np.uint8)
+    seen = np.zeros(4, np.int64)
+    for now in (ts(2026, 3, 29, 12), ts(2026, 7, 15, 3, 7, 9), ts(2026, 10, 25, 0, 59, 59), ts(2026, 11, 1, 6), ts(2027, 1, 1)):
+        earliest = now - synth.gen_times(n, -7200, 20 * 86400, seed=int(now % 1000))
+        got = shim.unmet(masks, earliest, now, zone_id=zid, klass_out=klass)
+        want = po.batch_unmet(masks, earliest, now, zone_id=zid, zone_names=NAMES)
+        _cmp(got, want, now)
+        seen += np.bincount(klass, minlength=4)
+    assert seen[1] > n and seen[2] > 1000 and seen[3] > 100, seen  # every path was exercised
+    # windows placed right against transitions of a DST zone
+    z = NAMES.index("Europe/Berlin")
+    when = shim.zone_entries(z)[0]
+    texts = ["* * * * *", "*/5 * * * *", "30 2 * * *", "0 0 * * *", "0 0 1 * *", "15 3 * * 0", "59 23 31 12 *", "0 12 1 1 *"]
+    base = _masks_of(texts)
+    S = len(texts)
+    for t in [int(w) for w in when if ts(2024) < w < ts(2028)]:
+        for back, ahead in [(40 * 86400, -33 * 86400), (40 * 86400, -1), (86400, -1), (3600, 3600), (10, 40 * 86400), (0, 86400)]:
+            zz = np.full(S, z, np.int32)
+            e, now = np.full(S, t - back), t + ahead
+            if now < t - back:
+                continue
+            _cmp(shim.unmet(base, e, now, zone_id=zz), po.batch_unmet(base, e, now, zone_id=zz, zone_names=NAMES), (t, back, ahead))
