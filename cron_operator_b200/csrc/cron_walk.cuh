@@ -832,4 +832,44 @@ CW_HD int64_t next_from_t(const Spec& s, Walk& w, int64_t t, bool resident) {
 }
 CW_HD int64_t next_from(const Spec& s, Walk& w, int64_t t, bool resident) { return next_from_t<false>(s, w, t, resident); }
 
+// ---- one zone period's local clock --------------------------------------------------------------------------------
+// Inside one constant-offset period local time is UTC moved by the offset.  When everything a computation can touch
+// lies inside the natural window of ONE period -- from the earliest Date() target upstream can make (the midnight of
+// the 1st of the starting month: at most 32 days back) to its last Next() result -- every Date() resolves naturally
+// and every Add-based stretch stays in the period, so upstream's walk is the UTC walk on that clock.
+//
+// period_clock: does the period in force 32 days before `lo` still hold `hi`?  (t_min / t_max: supported absolute
+// range; zoned_max: zoned evaluations must start below it.)  *shift = the period's offset, *nhi = end of its natural
+// window on the local clock; the caller must still check that its results stay below *nhi.  Invalid ids and anything
+// doubtful say no: the general path decides and reports.
+CW_HD bool period_clock(const ZoneTable& zt, int32_t zone, int64_t lo, int64_t hi, int64_t t_min, int64_t t_max,
+                        int64_t zoned_max, int32_t* shift, int64_t* nhi) {
+  if (zone <= 0 || zone >= zt.nzones) return false;
+  if (lo < t_min + 33 * 86400LL || hi > t_max) return false;
+  Walk w;
+  w.bind_zone(zt, zone);
+  if (w.zn > 1 && hi >= zoned_max) return false;
+  const int32_t off = w.lookup(lo - 32 * 86400LL);
+  if (!(hi < w.pe) || off % 60 != 0) return false;
+  *shift = off;
+  *nhi = w.nhi;
+  return true;
+}
+
+// k chained Next() calls after `from` on a period's clock (shift, nhi from period_clock): true = out[0..k) holds the
+// fire times; false = some call left the period (or found nothing within five years, i.e. searched beyond it) and the
+// general walk must answer.
+CW_HD bool next_n_on_period_clock(const Spec& s, int64_t from, int k, int32_t shift, int64_t nhi, int64_t* out) {
+  Walk w;
+  w.bind_utc();
+  if (!s.never) w.tod_last = spec_tod_last(s);
+  int64_t t = from + shift;
+  for (int j = 0; j < k; ++j) {
+    t = next_from_t<false, true>(s, w, t, j > 0);
+    if (t == kZero || t >= nhi) return false;
+    out[j] = t - shift;
+  }
+  return true;
+}
+
 }  // namespace cronwalk

@@ -188,11 +188,20 @@ constexpr int kNextTileSpecs = 512;
 #define B200CRON_NEXTN_ZONED_MINBLOCKS 6
 #endif
 
+// A row whose first entry is kNextRejected was handed over by the class-A launch: its chain left the zone period it
+// started in, and the zoned launch (which runs next on the stream) walks it with the general code.
+constexpr int64_t kNextRejected = INT64_MIN + 1;  // never a result: results are >= kMinTime, or kZero
+
 template <int KT, bool kUtc>
 __global__ void __launch_bounds__(kNextTileThreads, kUtc ? B200CRON_NEXTN_UTC_MINBLOCKS : B200CRON_NEXTN_ZONED_MINBLOCKS)
 next_n_tile_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* __restrict__ from, size_t n, int k_rt,
-                   int64_t* __restrict__ out, ZoneTable zt, int* __restrict__ err) {
+                   int64_t* out, ZoneTable zt, int* __restrict__ err) {
+  // kUtc launch = class A: specs evaluated in UTC, and zoned specs whose start lies 32 days inside one zone period --
+  // their chain runs on that period's clock (cronwalk::period_clock) and is rejected if a fire leaves the period.
+  // The other launch = everything else: zoned specs near a transition, and the rejected rows.
   __shared__ uint16_t s_idx[kNextTileSpecs];
+  __shared__ int32_t s_shift[kUtc ? kNextTileSpecs : 1];
+  __shared__ int64_t s_nhi[kUtc ? kNextTileSpecs : 1];
   __shared__ int s_n;
   const int k = KT > 0 ? KT : k_rt;
   const size_t base = (size_t)blockIdx.x * kNextTileSpecs;
@@ -202,15 +211,27 @@ next_n_tile_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int6
   if (zone_id != nullptr) {
     if (threadIdx.x == 0) s_n = 0;
     __syncthreads();
-#pragma unroll
+#pragma unroll 1
     for (int it = 0; it < kNextTileSpecs / kNextTileThreads; ++it) {
       const int q = it * kNextTileThreads + threadIdx.x;
-      const bool take = q < cnt && ((__ldg(zone_id + base + q) == 0) == kUtc);
+      bool take = false;
+      int32_t shift = 0;
+      int64_t nhi = cronwalk::kOmega;
+      if (q < cnt) {
+        const int32_t z = __ldg(zone_id + base + q);
+        const int64_t f = __ldg(from + base + q);
+        const bool cls_a = z == 0 || cronwalk::period_clock(zt, z, f, f, kMinTime, kMaxTime, zt.horizon - kSixYears, &shift, &nhi);
+        take = kUtc ? cls_a : (!cls_a || (z != 0 && out[(base + q) * (size_t)k] == kNextRejected));
+      }
       const unsigned mk = __ballot_sync(0xffffffffu, take);
       int b = 0;
       if (lane == 0 && mk) b = atomicAdd(&s_n, __popc(mk));
       b = __shfl_sync(0xffffffffu, b, 0);
-      if (take) s_idx[b + __popc(mk & ((1u << lane) - 1u))] = (uint16_t)q;
+      if (take) {
+        const int slot = b + __popc(mk & ((1u << lane) - 1u));
+        s_idx[slot] = (uint16_t)q;
+        if (kUtc) { s_shift[slot] = shift; s_nhi[slot] = nhi; }
+      }
     }
     __syncthreads();
     mine = s_n;
@@ -224,10 +245,15 @@ next_n_tile_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int6
                                         __ldg(m.p[3] + i), __ldg(m.p[4] + i), __ldg(m.p[5] + i));
     int64_t t = __ldg(from + i);
     const int32_t zone = kUtc ? 0 : __ldg(zone_id + i);
+    const int32_t shift = (kUtc && live && zone_id && !ss.every) ? s_shift[q] : 0;
+    const int64_t nhi = (kUtc && live && zone_id && !ss.every) ? s_nhi[q] : cronwalk::kOmega;
+    const bool on_period = kUtc && (shift != 0 || nhi != cronwalk::kOmega);
     Walk w;
     bool ok = live && bind_checked(w, zt, zone, t, err);
     if (!live) w.bind_utc();
     if (!ss.never) w.tod_last = cronwalk::spec_tod_last(ss);  // lets chained calls skip exhausted days
+    t += shift;  // onto the period's clock (0 for UTC)
+    bool left = false;
     int64_t* row = out + i * (size_t)k;
     // compile-time even k and a 16-byte aligned output: results leave two at a time (half the store instructions)
     const bool pair = B200CRON_NEXTN_PAIR && KT > 0 && (KT & 1) == 0 && (reinterpret_cast<uintptr_t>(out) & 15u) == 0;
@@ -235,19 +261,23 @@ next_n_tile_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int6
 #pragma unroll 1
     for (int j = 0; j < k; ++j) {
       __syncwarp();  // every lane runs exactly k iterations: re-converge, or lanes on a short path run ahead for good
+      int64_t r = kZero;
       if (ok && t != kZero) {
         t = cronwalk::next_from_t<false, kUtc>(ss, w, t, j > 0);
         if (!kUtc && t != kZero && !ss.every && w.zn > 1 && t >= zt.horizon - kSixYears) { atomicOr(err, kErrRange); ok = false; t = kZero; }
+        if (on_period) left = left || t == kZero || t >= nhi;  // the chain left its period: the general walk answers
+        r = t == kZero ? kZero : t - shift;
       } else {
         t = kZero;
       }
       if (pair) {
-        if (j & 1) { if (live) *reinterpret_cast<longlong2*>(row + j - 1) = make_longlong2(held, t); }
-        else held = t;
+        if (j & 1) { if (live) *reinterpret_cast<longlong2*>(row + j - 1) = make_longlong2(held, r); }
+        else held = r;
       } else if (live) {
-        row[j] = t;
+        row[j] = r;
       }
     }
+    if (kUtc && live && left) row[0] = kNextRejected;
   }
 }
 

@@ -365,28 +365,11 @@ CW_HD void unmet_step_utc(const Spec& s, const UnmetIn& in, UnmetState& st) {
   st.resident = true;
 }
 
-// ---- the UTC machine on one zone period's local clock -----------------------------------------------------------
-// Inside one constant-offset period local time is UTC moved by the offset.  When a Cron's whole window lies inside
-// the natural window of ONE period -- from the earliest Date() target upstream can make (the midnight of the 1st of
-// earliest's month at the latest 32 days back) to the last Next() result -- every Date() resolves naturally and every
-// Add-based stretch stays in the period, so upstream's walk is the UTC walk on that clock.
-//
-// unmet_class_a: does the period in force 32 days before min(earliest, now) still hold now?  (t_min / t_max: supported
-// absolute range; zoned_max: zoned evaluations must start below it.)  *shift = the period's offset, *nhi = end of its
-// natural window on the local clock.  Invalid ids and anything doubtful say no: the general path decides and reports.
+// ---- the UTC machine on one zone period's local clock (cron_walk.cuh: period_clock) ---------------------------------
+// unmet_class_a: the Cron's window runs from min(earliest, now) to now
 CW_HD bool unmet_class_a(const ZoneTable& zt, int32_t zone, int64_t earliest, int64_t now, int64_t t_min, int64_t t_max,
                          int64_t zoned_max, int32_t* shift, int64_t* nhi) {
-  if (zone <= 0 || zone >= zt.nzones) return false;
-  const int64_t lo = earliest < now ? earliest : now;
-  if (lo < t_min + 33 * 86400LL || now > t_max) return false;
-  Walk w;
-  w.bind_zone(zt, zone);
-  if (w.zn > 1 && now >= zoned_max) return false;
-  const int32_t off = w.lookup(lo - 32 * 86400LL);
-  if (!(now < w.pe) || off % 60 != 0) return false;
-  *shift = off;
-  *nhi = w.nhi;
-  return true;
+  return period_clock(zt, zone, earliest < now ? earliest : now, now, t_min, t_max, zoned_max, shift, nhi);
 }
 // gates on the real clock, then `in` moves onto the local clock and the UTC machine starts
 CW_HD void unmet_begin_shifted(const ZoneTable& zt, UnmetIn& in, int32_t shift, UnmetState& st) {

@@ -61,6 +61,14 @@ void shim_next_n(void* table, const uint64_t* const masks[6], const int32_t* zon
     if (k != 1 && !s.never) w.tod_last = spec_tod_last(s);  // as next_n_kernel does
     int64_t t = from[i];
     bool resident = false;
+    // as next_n_tile_kernel does: a zoned spec deep inside one zone period runs on that period's clock, and falls
+    // back to the general walk when its chain leaves the period
+    int32_t shift = 0;
+    int64_t nhi = kOmega;
+    if (k > 1 && z != 0 && !s.every &&
+        period_clock(zt, z, t, t, -62135596800LL, 253402300799LL, zt.horizon - 6LL * 366 * 86400, &shift, &nhi) &&
+        next_n_on_period_clock(s, t, k, shift, nhi, out + i * (size_t)k))
+      continue;
     for (int q = 0; q < k; ++q) {
       if (t != kZero) {
         // zone_id == NULL: the all-UTC specialisation, as next1_kernel<true> is chosen for launches without zone ids
