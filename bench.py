@@ -194,12 +194,13 @@ def c3_c4(ctx, torch, st, peak, flush, clocks):
     o4 = dict(last=torch.empty(n4, dtype=torch.int64, device="cuda"), next=torch.empty(n4, dtype=torch.int64, device="cuda"),
               missed=torch.empty(n4, dtype=torch.int32, device="cuda"), status=torch.empty(n4, dtype=torch.uint8, device="cuda"),
               decision=torch.empty(n4, dtype=torch.uint8, device="cuda"))
-    s = timed(torch, lambda: ctx.unmet_since_dev(dm4, de4, now, o4, 0, dp, da, dfl, ddl, dz4, stream=st), flush=flush)
+    # C4's specs are 5-field (C2's distribution): no seconds plane is passed (second 0, as ParseStandard yields)
+    s = timed(torch, lambda: ctx.unmet_since_dev(dm4, de4, now, o4, 0, dp, da, dfl, ddl, dz4, stream=st, five_field=True), flush=flush)
     ctx.sync_check(stream=st)
     missed_total = int(o4["missed"].to(torch.int64).sum().item())
     ipc = NCU.get("unmet_warp_inst_per_cron")
-    c4 = {"specs": n4, "specs_per_s": n4 / s, "ms": s * 1e3, "bytes_per_spec": 96,
-          "roofline_frac": 96 * n4 / s / 1e9 / peak,
+    c4 = {"specs": n4, "specs_per_s": n4 / s, "ms": s * 1e3, "bytes_per_spec": 88,
+          "roofline_frac": 88 * n4 / s / 1e9 / peak,
           "issue_frac": issue_frac(ipc, n4, s, clocks) if ipc else None, "warp_inst_per_cron": ipc,
           "issue_source": NCU.get("unmet_source"), "missed_runs_counted": missed_total,
           "equivalent_literal_next_calls_per_s": (missed_total + 2 * n4) / s,
@@ -215,7 +216,7 @@ def c3_c4(ctx, torch, st, peak, flush, clocks):
     hm.array[:] = m4; hz.array[:] = z4; he.array[:] = e4; hp.array[:] = pol4; ha.array[:] = act4; hf.array[:] = fl4; hd.array[:] = dl4
     owners = dict(last=P(n4, np.int64), next=P(n4, np.int64), missed=P(n4, np.uint32), status=P(n4, np.uint8), decision=P(n4, np.uint8))
     ho = {k_: v.array for k_, v in owners.items()}
-    call = lambda: ctx.unmet_since(hm.array, he.array, now, 0, hp.array, ha.array, hf.array, hd.array, hz.array, out=ho)  # noqa: E731
+    call = lambda: ctx.unmet_since(hm.array, he.array, now, 0, hp.array, ha.array, hf.array, hd.array, hz.array, out=ho, five_field=True)  # noqa: E731
     call()
     best = 1e30
     for _ in range(3):
@@ -223,10 +224,10 @@ def c3_c4(ctx, torch, st, peak, flush, clocks):
         call()
         best = min(best, time.perf_counter() - t0)
     same = all(np.array_equal(ho[k_], dev_out[k_].view(ho[k_].dtype)) for k_ in ho)
-    c4["e2e"] = {"specs_per_s": n4 / best, "ms": best * 1e3, "h2d_bytes": 74 * n4, "d2h_bytes": 22 * n4,
+    c4["e2e"] = {"specs_per_s": n4 / best, "ms": best * 1e3, "h2d_bytes": 66 * n4, "d2h_bytes": 22 * n4,
                  "matches_device_path": bool(same),
-                 "how": "b200cron_unmet_since on pinned host buffers (kernels work on them in place over PCIe), wall clock"}
-    sset = ctx.specset(m4, z4)
+                 "how": "b200cron_unmet_since on pinned host buffers (staged chunk copies + kernels + copies back), wall clock"}
+    sset = ctx.specset(m4, z4, five_field=True)
     call = lambda: sset.unmet_since(he.array, now, 0, hp.array, ha.array, hf.array, hd.array, out=ho)  # noqa: E731
     call()
     best = 1e30

@@ -287,8 +287,8 @@ class Context:
         return out
 
     def unmet_since(self, masks: np.ndarray, earliest, now: int, now_nsec: int = 0, policy=None, active=None,
-                    flags=None, deadline=None, zone_id=None, out=None) -> dict:
-        planes, n = _planes(masks)
+                    flags=None, deadline=None, zone_id=None, out=None, five_field: bool = False) -> dict:
+        planes, n = _planes(masks, five_field)
         cv = lambda a, dt: None if a is None else np.ascontiguousarray(a, dtype=dt)  # noqa: E731
         earliest = cv(earliest, np.int64)
         zid, policy, active = cv(zone_id, np.int32), cv(policy, np.uint8), cv(active, np.uint32)
@@ -359,8 +359,8 @@ class Context:
                                               n, k, _ptr(out)))
 
     def unmet_since_dev(self, masks, earliest, now, out: dict, now_nsec=0, policy=None, active=None, flags=None,
-                        deadline=None, zone_id=None, dev_index: int = 0, stream: int = 0):
-        planes, n = _planes(masks)
+                        deadline=None, zone_id=None, dev_index: int = 0, stream: int = 0, five_field: bool = False):
+        planes, n = _planes(masks, five_field)
         self._check(lib().b200cron_unmet_since_dev(self._h, dev_index, stream or None, planes, _ptr(zone_id),
                                                    _ptr(earliest), now, now_nsec, _ptr(policy), _ptr(active),
                                                    _ptr(flags), _ptr(deadline), n, _ptr(out["last"]),

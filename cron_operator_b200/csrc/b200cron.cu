@@ -163,6 +163,9 @@ cudaError_t launch_next_kt(bool vec, unsigned grid, size_t smem, cudaStream_t st
   return cudaGetLastError();
 }
 
+#ifndef B200CRON_NEXT1_FIVE
+#define B200CRON_NEXT1_FIVE 1  // 0 (tuning builds): launches without a seconds plane use the general instantiation
+#endif
 // B200CRON_NEXT1_RING (tuning builds): 1 = k == 1 launches on device-resident inputs use the persistent kernel with the
 // asynchronous input ring (next1_ring_kernel); 0 = always next1_kernel.  Measured on B200 (profiles/README.md, r2c):
 // the ring is bit-exact through the whole GPU suite but SLOWER -- 18.8 vs 13.7 us per 1M specs with overlapping
@@ -207,8 +210,13 @@ cudaError_t launch_next(b200cron_ctx* ctx, const Device& d, cudaStream_t st, con
 #else
     (void)device_resident;
 #endif
-    if (zone) return cudaLaunchKernelEx(&cfg, next1_kernel<false>, m, zone, from, n, out, d.zt, err);
-    return cudaLaunchKernelEx(&cfg, next1_kernel<true>, m, zone, from, n, out, d.zt, err);  // all-UTC launch
+    const bool five = B200CRON_NEXT1_FIVE && m.p[0] == nullptr;  // no seconds plane: the 5-field instantiation
+    if (zone) {
+      if (five) return cudaLaunchKernelEx(&cfg, next1_kernel<false, true>, m, zone, from, n, out, d.zt, err);
+      return cudaLaunchKernelEx(&cfg, next1_kernel<false, false>, m, zone, from, n, out, d.zt, err);
+    }
+    if (five) return cudaLaunchKernelEx(&cfg, next1_kernel<true, true>, m, zone, from, n, out, d.zt, err);  // all-UTC launch
+    return cudaLaunchKernelEx(&cfg, next1_kernel<true, false>, m, zone, from, n, out, d.zt, err);
   }
 #if B200CRON_NEXTN_SPLIT
   {  // k > 1: class-pure warps, one launch per class (kernels.cuh); a launch without zone ids is all UTC
@@ -252,7 +260,8 @@ cudaError_t launch_unmet(b200cron_ctx* ctx, Device& d, cudaStream_t st, const Un
   const unsigned tiles = (unsigned)((a.n + kUnmetTile - 1) / kUnmetTile);
   if (!a.zone_id) {  // every Cron in UTC: the closed form always answers, nothing can be deferred, no scratch
     ctx->launches.fetch_add(1, std::memory_order_relaxed);
-    unmet_tile_kernel<false><<<tiles, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, nullptr, nullptr, nullptr, nullptr);
+    if (a.m.p[0]) unmet_tile_kernel<false, false><<<tiles, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, nullptr, nullptr, nullptr, nullptr);
+    else unmet_tile_kernel<false, true><<<tiles, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, nullptr, nullptr, nullptr, nullptr);
     return cudaGetLastError();
   }
   DeferList& b = d.defer[d.defer_next];
@@ -290,7 +299,8 @@ cudaError_t launch_unmet(b200cron_ctx* ctx, Device& d, cudaStream_t st, const Un
     if ((e = cudaMemsetAsync(b.count, 0, (size_t)(nz + 2) * sizeof(uint32_t), st)) != cudaSuccess) return e;
     const unsigned zgrid = (unsigned)((a.n + kZoneOrderTile - 1) / kZoneOrderTile);
     ctx->launches.fetch_add(6, std::memory_order_relaxed);
-    unmet_tile_kernel<false><<<tiles, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, nullptr, nullptr, z1_list, z1_count);
+    if (a.m.p[0]) unmet_tile_kernel<false, false><<<tiles, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, nullptr, nullptr, z1_list, z1_count);
+    else unmet_tile_kernel<false, true><<<tiles, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, nullptr, nullptr, z1_list, z1_count);
     zone_order_hist_kernel<<<zgrid, kZoneOrderThreads, (size_t)nz * sizeof(uint32_t), st>>>(a.zone_id, z1_list, z1_count, nz, hist);
     zone_order_scan_kernel<<<1, kZoneOrderThreads, 0, st>>>(hist, nz, cursor);
     zone_order_scatter_kernel<<<zgrid, kZoneOrderThreads, 2 * (size_t)nz * sizeof(uint32_t), st>>>(a.zone_id, z1_list, z1_count,
@@ -300,7 +310,7 @@ cudaError_t launch_unmet(b200cron_ctx* ctx, Device& d, cudaStream_t st, const Un
   } else {
     if ((e = cudaMemsetAsync(b.count, 0, sizeof(uint32_t), st)) != cudaSuccess) return e;
     ctx->launches.fetch_add(2, std::memory_order_relaxed);
-    unmet_tile_kernel<true><<<tiles, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, b.idx, b.count, nullptr, nullptr);
+    unmet_tile_kernel<true, false><<<tiles, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, b.idx, b.count, nullptr, nullptr);
   }
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
   const unsigned hard_max = (unsigned)d.sm_count * B200CRON_UNMET_HARD_MINBLOCKS;

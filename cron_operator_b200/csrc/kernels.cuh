@@ -188,8 +188,9 @@ constexpr int kNextTileSpecs = 512;
 #define B200CRON_NEXTN_ZONED_MINBLOCKS 6
 #endif
 
-// A row whose first entry is kNextRejected was handed over by the class-A launch: its chain left the zone period it
-// started in, and the zoned launch (which runs next on the stream) walks it with the general code.
+// A row whose first entry is kNextRejected was handed over by the class-A launch -- a zoned spec near a transition, or a
+// chain that left the zone period it started in -- and the zoned launch (next on the stream) walks it with the general
+// code.
 constexpr int64_t kNextRejected = INT64_MIN + 1;  // never a result: results are >= kMinTime, or kZero
 
 template <int KT, bool kUtc>
@@ -219,9 +220,14 @@ next_n_tile_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int6
       int64_t nhi = cronwalk::kOmega;
       if (q < cnt) {
         const int32_t z = __ldg(zone_id + base + q);
-        const int64_t f = __ldg(from + base + q);
-        const bool cls_a = z == 0 || cronwalk::period_clock(zt, z, f, f, kMinTime, kMaxTime, zt.horizon - kSixYears, &shift, &nhi);
-        take = kUtc ? cls_a : (!cls_a || (z != 0 && out[(base + q) * (size_t)k] == kNextRejected));
+        if (kUtc) {
+          // class A?  Everything else is handed to the zoned launch by the same mark a rejected chain gets.
+          take = z == 0 || cronwalk::period_clock(zt, z, __ldg(from + base + q), __ldg(from + base + q), kMinTime, kMaxTime,
+                                                  zt.horizon - kSixYears, &shift, &nhi);
+          if (!take) out[(base + q) * (size_t)k] = kNextRejected;
+        } else {
+          take = z != 0 && out[(base + q) * (size_t)k] == kNextRejected;
+        }
       }
       const unsigned mk = __ballot_sync(0xffffffffu, take);
       int b = 0;
@@ -295,7 +301,10 @@ next_n_tile_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int6
 #endif
 constexpr int kNext1Threads = B200CRON_NEXT1_THREADS;
 
-template <bool kUtcOnly>
+// kFive: the launch has no seconds plane (5-field schedules, the only kind ParseStandard builds: second 0).  The
+// seconds mask is then the compile-time constant 1 and everything derived from it folds away (first matching second,
+// the seconds search of next_tod_ge, the sentinel scans of make_spec).
+template <bool kUtcOnly, bool kFive>
 __global__ void __launch_bounds__(kNext1Threads, B200CRON_NEXT1_MINBLOCKS)
 next1_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* __restrict__ from, size_t n,
              int64_t* __restrict__ out, ZoneTable zt, int* __restrict__ err) {
@@ -305,7 +314,7 @@ next1_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* _
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const size_t i = (size_t)blockIdx.x * kNext1Threads + threadIdx.x;
   if (i >= n) { asm volatile("griddepcontrol.wait;" ::: "memory"); return; }
-  const Spec s = cronwalk::make_spec(m.p[0] ? __ldg(m.p[0] + i) : 1ULL, __ldg(m.p[1] + i), __ldg(m.p[2] + i), __ldg(m.p[3] + i),
+  const Spec s = cronwalk::make_spec(kFive ? 1ULL : (m.p[0] ? __ldg(m.p[0] + i) : 1ULL), __ldg(m.p[1] + i), __ldg(m.p[2] + i), __ldg(m.p[3] + i),
                                      __ldg(m.p[4] + i), __ldg(m.p[5] + i));
   const int64_t t = __ldg(from + i);
   const int32_t zone = (!kUtcOnly && zone_id) ? __ldg(zone_id + i) : 0;
@@ -509,15 +518,16 @@ constexpr int kUnmetEasyRounds = B200CRON_UNMET_EASY_ROUNDS;
 // so the UTC machine runs on the local clock and the answers are moved back.  `nhi` bounds the period's natural window
 // on that clock: a Next() beyond it (or one that found nothing in five years) left the period, the lane is then
 // *rejected -- nothing is written -- and the caller hands the Cron to the general path.
-template <int kMode>
+// kFive: the launch has no seconds plane (5-field schedules): the seconds mask is the constant 1 and folds away.
+template <int kMode, bool kFive = false>
 __device__ __forceinline__ void unmet_one(const UnmetArgs& a, const ZoneTable& zt, int* __restrict__ err, size_t i,
                                           bool live, uint32_t* __restrict__ defer_idx,
                                           uint32_t* __restrict__ defer_count, int32_t shift = 0,
                                           int64_t nhi = cronwalk::kOmega, bool* rejected = nullptr) {
   const size_t ii = live ? i : 0;  // out-of-range lanes stay in the warp-uniform loop below, doing nothing
   // masks[0] == NULL: 5-field schedules, second 0 (what ParseStandard always yields)
-  const Spec s = cronwalk::make_spec(a.m.p[0] ? __ldg(a.m.p[0] + ii) : 1ULL, __ldg(a.m.p[1] + ii), __ldg(a.m.p[2] + ii),
-                                     __ldg(a.m.p[3] + ii), __ldg(a.m.p[4] + ii), __ldg(a.m.p[5] + ii));
+  const Spec s = cronwalk::make_spec(kFive ? 1ULL : (a.m.p[0] ? __ldg(a.m.p[0] + ii) : 1ULL), __ldg(a.m.p[1] + ii),
+                                     __ldg(a.m.p[2] + ii), __ldg(a.m.p[3] + ii), __ldg(a.m.p[4] + ii), __ldg(a.m.p[5] + ii));
   cronwalk::UnmetIn in;
   in.earliest = __ldg(a.earliest + ii);
   in.now = a.now;
@@ -607,7 +617,7 @@ unmet_single_kernel(UnmetArgs a, ZoneTable zt, int* __restrict__ err) {
 // otherwise they are appended to `z1_list` for the zone-ordered kernel.  A launch without zone ids is all class A: no
 // classification, no lists.
 constexpr int kUnmetTile = 512;  // Crons per CTA: ~12 + 4 warps' worth on a half-UTC workload
-template <bool kZoned>
+template <bool kZoned, bool kFive>
 __global__ void __launch_bounds__(kUnmetThreads, B200CRON_UNMET_EASY_MINBLOCKS)
 unmet_tile_kernel(UnmetArgs a, ZoneTable zt, int* __restrict__ err, uint32_t* __restrict__ defer_idx,
                   uint32_t* __restrict__ defer_count, uint32_t* __restrict__ z1_list, uint32_t* __restrict__ z1_count) {
@@ -659,7 +669,7 @@ unmet_tile_kernel(UnmetArgs a, ZoneTable zt, int* __restrict__ err, uint32_t* __
     const bool plain = a.zone_id == nullptr;
     const int li = live ? (plain ? q : (int)s_idx[q]) : 0;
     bool rejected = false;
-    unmet_one<kUnmetUtc>(a, zt, err, base + li, live, nullptr, nullptr, (live && !plain) ? s_shift[q] : 0,
+    unmet_one<kUnmetUtc, kFive>(a, zt, err, base + li, live, nullptr, nullptr, (live && !plain) ? s_shift[q] : 0,
                          (live && !plain) ? s_nhi[q] : cronwalk::kOmega, &rejected);
     const unsigned mr = __ballot_sync(0xffffffffu, rejected);
     if (mr) {

@@ -31,7 +31,7 @@ if which == "next1":
     for b in range(nb):
         ctx.synth_specs_dev(dm[b], n1, 0xC0FFEE, b * n1, False, stream=st)
         ctx.synth_times_dev(df[b], n1, synth.ts(2024), synth.ts(2034), 0xC0FFEE, b * n1, stream=st)
-    planes = [api._planes(x)[0] for x in dm]
+    planes = [api._planes(x, five_field=not os.environ.get("SIX"))[0] for x in dm]  # SIX=1: pass the seconds plane too
     L = api.lib()
     for ov in (1, 0):
         ctx.set_overlap(bool(ov))
@@ -61,7 +61,8 @@ if which == "unmet":
     o = dict(last=torch.empty(n, dtype=torch.int64, device="cuda"), next=torch.empty(n, dtype=torch.int64, device="cuda"),
              missed=torch.empty(n, dtype=torch.int32, device="cuda"), status=torch.empty(n, dtype=torch.uint8, device="cuda"),
              decision=torch.empty(n, dtype=torch.uint8, device="cuda"))
-    fn = lambda: ctx.unmet_since_dev(dm, de, now, o, 0, dp, da, dfl, ddl, dz, stream=st)  # noqa: E731
+    five = bool(os.environ.get("FIVE"))  # FIVE=1: no seconds plane (5-field schedules)
+    fn = lambda: ctx.unmet_since_dev(dm, de, now, o, 0, dp, da, dfl, ddl, dz, stream=st, five_field=five)  # noqa: E731
 elif which == "nextn":
     m = synth.gen_specs(n, seed=3, with_seconds=True)
     z = synth.gen_zone_ids(n, len(names), dst, seed=3)
