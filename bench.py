@@ -380,7 +380,7 @@ def main():
     # on the device by global index (bit-identical to synth.py).  Launches rotate through the batches, so a batch's
     # 64 MB were last touched N_BATCH-1 launches (448 MB of other traffic) ago and are gone from the 126 MB L2.
     base = rank * N_BATCH * N_SPECS
-    d_masks, d_from, d_out, planes = [], [], [], []
+    d_masks, d_from, d_out, planes, planes5 = [], [], [], [], []
     for b in range(N_BATCH):
         dm = torch.empty((6, N_SPECS), dtype=torch.int64, device="cuda")
         df = torch.empty(N_SPECS, dtype=torch.int64, device="cuda")
@@ -389,7 +389,8 @@ def main():
         d_masks.append(dm)
         d_from.append(df)
         d_out.append(torch.empty((N_SPECS, 1), dtype=torch.int64, device="cuda"))
-        planes.append(api._planes(dm, five_field=True)[0])  # 5-field schedules: no seconds plane (second 0)
+        planes.append(api._planes(dm)[0])                    # all six planes: the 64 B/eval of SURVEY.md 8d really move
+        planes5.append(api._planes(dm, five_field=True)[0])  # the same specs as a 5-field caller passes them (no seconds plane)
     ctx.sync_check(stream=st)
     masks = synth.gen_specs(N_SPECS, start=base)
     frm = synth.gen_times(N_SPECS, T_LO, T_HI, start=base)
@@ -403,8 +404,8 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    def launch(b):  # the C-ABI call, with the argument marshalling hoisted out of the timed loop
-        rc = L.b200cron_next_n_dev(ctx._h, 0, st, planes[b], None, d_from[b].data_ptr(), N_SPECS, 1, d_out[b].data_ptr())
+    def launch(b, pl=None):  # the C-ABI call, with the argument marshalling hoisted out of the timed loop
+        rc = L.b200cron_next_n_dev(ctx._h, 0, st, (pl or planes)[b], None, d_from[b].data_ptr(), N_SPECS, 1, d_out[b].data_ptr())
         if rc != 0:
             ctx._check(rc)
 
@@ -446,6 +447,17 @@ def main():
         ctx.sync_check(stream=st)
         serial_us = s0.elapsed_time(s1) / (min(args.steps, 5) * STEP_BATCHES) * 1e3
         ctx.set_overlap(True)
+    # the same launches as a 5-field caller makes them: no seconds plane (second 0 is all ParseStandard can produce), so
+    # 56 B/eval move and the kernel's 5-field instantiation runs
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for j in range(N_BATCH):
+        launch(j, planes5)
+    f0.record()
+    for j in range(5 * STEP_BATCHES):
+        launch(j % N_BATCH, planes5)
+    f1.record()
+    ctx.sync_check(stream=st)
+    five_us = f0.elapsed_time(f1) / (5 * STEP_BATCHES) * 1e3
     # cross-check: the same kernel timed one launch at a time with the L2 flushed before each (includes launch latency)
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(30)]
     for i, (a, b) in enumerate(ev):
@@ -531,6 +543,10 @@ def main():
                          "frac_overlap_off": (BYTES_PER_EVAL * N_SPECS / (serial_us * 1e-6) / 1e9 / peak) if serial_us else None,
                          "issue_frac": issue_frac(ipe, N_SPECS, avg_launch_s, clocks) if ipe else None,
                          "warp_inst_per_eval": ipe,
+                         "five_field_launch": {"us_per_launch": five_us, "evals_per_s_per_gpu": N_SPECS / (five_us * 1e-6),
+                                               "bytes_per_eval": 56, "frac": 56 * N_SPECS / (five_us * 1e-6) / 1e9 / peak,
+                                               "note": "same specs without the seconds plane (NULL = second 0), 5-field "
+                                                       "instantiation; this GPU only, not max over ranks"},
                          "flushed_single_launch_us_min_med_max": [min(kernel_us), float(np.median(kernel_us)), max(kernel_us)],
                          "note": "cross-check: one launch at a time after a 256 MiB L2 flush, includes launch latency"},
             "clocks": clocks,

@@ -187,6 +187,7 @@ cudaError_t launch_next(b200cron_ctx* ctx, const Device& d, cudaStream_t st, con
   const size_t smem = (k == 1 || !kNextStage) ? 0 : (size_t)kNextTile * k * sizeof(int64_t);
   ctx->launches.fetch_add(1, std::memory_order_relaxed);
   if (k == 1) {  // one spec per lane (finer waves than next_n_kernel's two)
+    if (n > 0xffffffffULL) return cudaErrorInvalidValue;  // next1_kernel indexes with 32 bits (4G specs = 240 GB of inputs)
     const unsigned g1 = (unsigned)((n + kNext1Threads - 1) / kNext1Threads);
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(g1);
@@ -226,7 +227,8 @@ cudaError_t launch_next(b200cron_ctx* ctx, const Device& d, cudaStream_t st, con
       next_n_tile_kernel<KT, true><<<tgrid, kNextTileThreads, 0, st>>>(m, zone, from, n, k, out, d.zt, d.d_err);
       if (zone) {
         ctx->launches.fetch_add(1, std::memory_order_relaxed);
-        next_n_tile_kernel<KT, false><<<tgrid, kNextTileThreads, 0, st>>>(m, zone, from, n, k, out, d.zt, d.d_err);
+        const unsigned zgrid = (unsigned)((n + kNextTileSpecsZoned - 1) / kNextTileSpecsZoned);
+        next_n_tile_kernel<KT, false><<<zgrid, kNextTileThreads, 0, st>>>(m, zone, from, n, k, out, d.zt, d.d_err);
       }
       return cudaGetLastError();
     };

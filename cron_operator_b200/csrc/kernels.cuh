@@ -177,7 +177,9 @@ next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* 
 // best).  A launch without zone ids is all UTC: no classification.
 // -------------------------------------------------------------------------------------------------------------
 constexpr int kNextTileThreads = 128;
-constexpr int kNextTileSpecs = 512;
+constexpr int kNextTileSpecs = 512;         // class-A launch: specs per CTA
+constexpr int kNextTileSpecsZoned = 2048;   // zoned launch: it takes ~7 % of the specs, so a CTA looks at four times as
+                                            // many to keep all of its warps busy (with 512 the launch was latency-bound)
 #ifndef B200CRON_NEXTN_UTC_MINBLOCKS
 #define B200CRON_NEXTN_UTC_MINBLOCKS 10
 #endif
@@ -200,20 +202,21 @@ next_n_tile_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int6
   // kUtc launch = class A: specs evaluated in UTC, and zoned specs whose start lies 32 days inside one zone period --
   // their chain runs on that period's clock (cronwalk::period_clock) and is rejected if a fire leaves the period.
   // The other launch = everything else: zoned specs near a transition, and the rejected rows.
-  __shared__ uint16_t s_idx[kNextTileSpecs];
-  __shared__ int32_t s_shift[kUtc ? kNextTileSpecs : 1];
-  __shared__ int64_t s_nhi[kUtc ? kNextTileSpecs : 1];
+  constexpr int kTile = kUtc ? kNextTileSpecs : kNextTileSpecsZoned;
+  __shared__ uint16_t s_idx[kTile];
+  __shared__ int32_t s_shift[kUtc ? kTile : 1];
+  __shared__ int64_t s_nhi[kUtc ? kTile : 1];
   __shared__ int s_n;
   const int k = KT > 0 ? KT : k_rt;
-  const size_t base = (size_t)blockIdx.x * kNextTileSpecs;
-  const int cnt = (int)((n - base) < (size_t)kNextTileSpecs ? (n - base) : (size_t)kNextTileSpecs);
+  const size_t base = (size_t)blockIdx.x * kTile;
+  const int cnt = (int)((n - base) < (size_t)kTile ? (n - base) : (size_t)kTile);
   const unsigned lane = threadIdx.x & 31u;
   int mine = cnt;
   if (zone_id != nullptr) {
     if (threadIdx.x == 0) s_n = 0;
     __syncthreads();
 #pragma unroll 1
-    for (int it = 0; it < kNextTileSpecs / kNextTileThreads; ++it) {
+    for (int it = 0; it < kTile / kNextTileThreads; ++it) {
       const int q = it * kNextTileThreads + threadIdx.x;
       bool take = false;
       int32_t shift = 0;
@@ -312,8 +315,10 @@ next1_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* _
   // (b200cron_ctx_set_overlap), the next launch on the stream may start filling SMs as soon as every CTA of this one
   // has got this far, instead of idling through this launch's last partial wave.  A no-op for ordinary launches.
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-  const size_t i = (size_t)blockIdx.x * kNext1Threads + threadIdx.x;
-  if (i >= n) { asm volatile("griddepcontrol.wait;" ::: "memory"); return; }
+  // 32-bit element index (the host keeps a launch below 2^32 specs): loads and the store address their arrays as
+  // uniform base + 32-bit offset instead of a 64-bit add per array
+  const uint32_t i = blockIdx.x * (uint32_t)kNext1Threads + threadIdx.x;
+  if (i >= (uint32_t)n) { asm volatile("griddepcontrol.wait;" ::: "memory"); return; }
   const Spec s = cronwalk::make_spec(kFive ? 1ULL : (m.p[0] ? __ldg(m.p[0] + i) : 1ULL), __ldg(m.p[1] + i), __ldg(m.p[2] + i), __ldg(m.p[3] + i),
                                      __ldg(m.p[4] + i), __ldg(m.p[5] + i));
   const int64_t t = __ldg(from + i);
