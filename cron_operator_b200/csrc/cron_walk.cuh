@@ -856,6 +856,26 @@ CW_HD bool period_clock(const ZoneTable& zt, int32_t zone, int64_t lo, int64_t h
   return true;
 }
 
+// period_clock for a chain of Next() calls starting at t, with the exact earliest Date() target instead of the 32-day
+// margin: upstream's first call resets to the midnight of (t+1s)'s day when only the day mismatches, or of the 1st of
+// its month when the month mismatches (month_mask = the spec's month plane); every later call starts on a fire, whose
+// month and day match, so its targets are never earlier.  The period holding t+1s must hold that midnight naturally.
+CW_HD bool period_clock_next(const ZoneTable& zt, int32_t zone, int64_t t, uint64_t month_mask, int64_t t_min, int64_t t_max,
+                             int64_t zoned_max, int32_t* shift, int64_t* nhi) {
+  if (zone <= 0 || zone >= zt.nzones) return false;
+  if (t < t_min + 33 * 86400LL || t > t_max) return false;
+  Walk w;
+  w.bind_zone(zt, zone);
+  if (w.zn > 1 && t >= zoned_max) return false;
+  w.load(t + 1);
+  if (w.off % 60 != 0) return false;
+  const int64_t x_lo = (int64_t)(((month_mask >> w.M) & 1ULL) ? w.dn : w.dn - (w.D - 1)) * 86400;
+  if (x_lo < w.nlo) return false;
+  *shift = w.off;
+  *nhi = w.nhi;
+  return true;
+}
+
 // k chained Next() calls after `from` on a period's clock (shift, nhi from period_clock): true = out[0..k) holds the
 // fire times; false = some call left the period (or found nothing within five years, i.e. searched beyond it) and the
 // general walk must answer.

@@ -199,8 +199,9 @@ template <int KT, bool kUtc>
 __global__ void __launch_bounds__(kNextTileThreads, kUtc ? B200CRON_NEXTN_UTC_MINBLOCKS : B200CRON_NEXTN_ZONED_MINBLOCKS)
 next_n_tile_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* __restrict__ from, size_t n, int k_rt,
                    int64_t* out, ZoneTable zt, int* __restrict__ err) {
-  // kUtc launch = class A: specs evaluated in UTC, and zoned specs whose start lies 32 days inside one zone period --
-  // their chain runs on that period's clock (cronwalk::period_clock) and is rejected if a fire leaves the period.
+  // kUtc launch = class A: specs evaluated in UTC, and zoned specs whose first Date() reset target lies naturally in
+  // the zone period of their start -- their chain runs on that period's clock (cronwalk::period_clock_next) and is
+  // rejected if a fire leaves the period.
   // The other launch = everything else: zoned specs near a transition, and the rejected rows.
   constexpr int kTile = kUtc ? kNextTileSpecs : kNextTileSpecsZoned;
   __shared__ uint16_t s_idx[kTile];
@@ -225,8 +226,8 @@ next_n_tile_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int6
         const int32_t z = __ldg(zone_id + base + q);
         if (kUtc) {
           // class A?  Everything else is handed to the zoned launch by the same mark a rejected chain gets.
-          take = z == 0 || cronwalk::period_clock(zt, z, __ldg(from + base + q), __ldg(from + base + q), kMinTime, kMaxTime,
-                                                  zt.horizon - kSixYears, &shift, &nhi);
+          take = z == 0 || cronwalk::period_clock_next(zt, z, __ldg(from + base + q), __ldg(m.p[4] + base + q), kMinTime,
+                                                       kMaxTime, zt.horizon - kSixYears, &shift, &nhi);
           if (!take) out[(base + q) * (size_t)k] = kNextRejected;
         } else {
           take = z != 0 && out[(base + q) * (size_t)k] == kNextRejected;
@@ -303,6 +304,9 @@ next_n_tile_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int6
 #define B200CRON_NEXT1_MINBLOCKS 16
 #endif
 constexpr int kNext1Threads = B200CRON_NEXT1_THREADS;
+#ifndef B200CRON_NEXT1_VOTE5
+#define B200CRON_NEXT1_VOTE5 1  // 0 (tuning builds): six-plane UTC launches always run the general walk
+#endif
 
 // kFive: the launch has no seconds plane (5-field schedules, the only kind ParseStandard builds: second 0).  The
 // seconds mask is then the compile-time constant 1 and everything derived from it folds away (first matching second,
@@ -319,13 +323,23 @@ next1_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* _
   // uniform base + 32-bit offset instead of a 64-bit add per array
   const uint32_t i = blockIdx.x * (uint32_t)kNext1Threads + threadIdx.x;
   if (i >= (uint32_t)n) { asm volatile("griddepcontrol.wait;" ::: "memory"); return; }
-  const Spec s = cronwalk::make_spec(kFive ? 1ULL : (m.p[0] ? __ldg(m.p[0] + i) : 1ULL), __ldg(m.p[1] + i), __ldg(m.p[2] + i), __ldg(m.p[3] + i),
-                                     __ldg(m.p[4] + i), __ldg(m.p[5] + i));
+  const uint64_t sec = kFive ? 1ULL : (m.p[0] ? __ldg(m.p[0] + i) : 1ULL);
+  const uint64_t mi = __ldg(m.p[1] + i), ho = __ldg(m.p[2] + i), dm = __ldg(m.p[3] + i), mo = __ldg(m.p[4] + i), dw = __ldg(m.p[5] + i);
   const int64_t t = __ldg(from + i);
   const int32_t zone = (!kUtcOnly && zone_id) ? __ldg(zone_id + i) : 0;
   Walk w;
   const bool ok = bind_checked(w, zt, zone, t, err);
-  const int64_t r = ok ? cronwalk::next_from_t<false, kUtcOnly>(s, w, t, false) : kZero;
+  int64_t r = kZero;
+  // A launch that does carry a seconds plane still runs the 5-field code when all of the warp's specs fire at second
+  // 0 only (what ParseStandard always yields; C2): the warp-uniform vote picks the copy of the walk in which the
+  // seconds mask is the constant 1.  UTC launches only: the zoned walk is too large to hold twice.
+  if (kFive || (kUtcOnly && B200CRON_NEXT1_VOTE5 && __all_sync(__activemask(), sec == 1ULL))) {
+    const Spec s = cronwalk::make_spec(1ULL, mi, ho, dm, mo, dw);
+    if (ok) r = cronwalk::next_from_t<false, kUtcOnly>(s, w, t, false);
+  } else {
+    const Spec s = cronwalk::make_spec(sec, mi, ho, dm, mo, dw);
+    if (ok) r = cronwalk::next_from_t<false, kUtcOnly>(s, w, t, false);
+  }
   // The other half of the programmatic launch: wait for the launch this one may have overlapped to complete (and
   // flush) before publishing anything.  Completion is then transitive along the stream -- when this grid has
   // finished, so has every earlier one -- which is what later stream work (copies, event records, other kernels)

@@ -28,8 +28,8 @@ for (lid, name), mm in launches.items():
     t = mm["gpu__time_duration.sum"][0] * tscale[mm["gpu__time_duration.sum"][1]]
     rd = mm["dram__bytes_read.sum"][0] * scale[mm["dram__bytes_read.sum"][1]]
     wr = mm["dram__bytes_write.sum"][0] * scale[mm["dram__bytes_write.sum"][1]]
-    alg = 64 * specs if "next1" in name else None
+    alg = 56 * specs if "next1" in name else None  # no seconds plane: 40 + 8 + 8 B per spec
     out.append(f"| {name[:48]} | {t * 1e3:.3f} ms | {rd / 1e9:.3f} GB | {wr / 1e9:.3f} GB | {(rd + wr) / t / 1e9:.0f} | "
-               f"{(rd + wr) / t / 1e9 / peak * 100:.1f} | {alg / t / 1e9:.0f}" + (" |" if alg else "- |"))
+               f"{(rd + wr) / t / 1e9 / peak * 100:.1f} | " + (f"{alg / t / 1e9:.0f} |" if alg else "- |"))
 open(f"profiles/r2_ncu_n{N}.md", "w").write("\n".join(out) + "\n")
 print("\n".join(out))

@@ -66,7 +66,7 @@ void shim_next_n(void* table, const uint64_t* const masks[6], const int32_t* zon
     int32_t shift = 0;
     int64_t nhi = kOmega;
     if (k > 1 && z != 0 && !s.every &&
-        period_clock(zt, z, t, t, -62135596800LL, 253402300799LL, zt.horizon - 6LL * 366 * 86400, &shift, &nhi) &&
+        period_clock_next(zt, z, t, masks[4][i], -62135596800LL, 253402300799LL, zt.horizon - 6LL * 366 * 86400, &shift, &nhi) &&
         next_n_on_period_clock(s, t, k, shift, nhi, out + i * (size_t)k))
       continue;
     for (int q = 0; q < k; ++q) {
