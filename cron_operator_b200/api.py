@@ -118,6 +118,8 @@ def lib(path: str | None = None):
     L.b200cron_next_n_set.argtypes = [vp, vp, vp, i32, vp]
     L.b200cron_unmet_since_set.restype = i32
     L.b200cron_unmet_since_set.argtypes = [vp, vp, vp, i64, C.c_int32, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+    L.b200cron_ctx_reserve_unmet.restype = i32
+    L.b200cron_ctx_reserve_unmet.argtypes = [vp, sz]
     L.b200cron_debug_last_deferred.restype = i32
     L.b200cron_debug_last_deferred.argtypes = [vp, i32, vp, vp, sz, C.POINTER(sz)]
     L.b200cron_sync_check.restype = i32
@@ -439,6 +441,10 @@ class Context:
         """b200cron_ctx_set_overlap: back-to-back k == 1 next_n_dev launches on one stream may overlap (the caller
         promises they are independent batches -- see include/b200cron.h)"""
         self._check(lib().b200cron_ctx_set_overlap(self._h, 1 if on else 0))
+
+    def reserve_unmet(self, max_n: int):
+        """allocate the unmet scratch for batches of up to max_n Crons per device now (no allocation inside a tick)"""
+        self._check(lib().b200cron_ctx_reserve_unmet(self._h, max_n))
 
     def last_deferred(self, cap: int = 1 << 24, dev_index: int = 0, stream: int = 0):
         """test support: (indices, count) of the Crons the most recent unmet launch handed to the general walk"""

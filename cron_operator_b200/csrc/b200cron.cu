@@ -629,6 +629,35 @@ extern "C" int b200cron_next_n(b200cron_ctx* ctx, const uint64_t* const masks[6]
 // =================================================================================================================
 // unmet_since
 // =================================================================================================================
+// Pre-sizes the unmet scratch (index lists + counters, all three buffers of every device) for batches of up to max_n
+// Crons per device, so that no b200cron_unmet_since* call allocates or frees device memory afterwards.
+extern "C" int b200cron_ctx_reserve_unmet(b200cron_ctx* ctx, size_t max_n) {
+  if (!ctx) return B200CRON_EINVAL;
+  if (max_n > 0xffffffffULL) return fail(ctx, B200CRON_EINVAL, "reserve_unmet: at most 2^32 - 1 Crons per device");
+  std::lock_guard<std::mutex> lk(ctx->mu);
+  for (Device& d : ctx->devs) {
+    CU(ctx, cudaSetDevice(d.id));
+    const size_t need = (B200CRON_UNMET_PLAN == 1 ? 3 : 1) * max_n;
+    for (DeferList& b : d.defer) {
+      if (!b.done) {
+        CU(ctx, cudaEventCreateWithFlags(&b.done, cudaEventDisableTiming));
+        CU(ctx, cudaMalloc(&b.count, (2 * (size_t)d.zt.nzones + 3) * sizeof(uint32_t)));
+      }
+      if (need > b.cap) {
+        if (b.idx) {
+          CU(ctx, cudaEventSynchronize(b.done));
+          CU(ctx, cudaFree(b.idx));
+          b.idx = nullptr;
+          b.cap = 0;
+        }
+        CU(ctx, cudaMalloc(&b.idx, need * sizeof(uint32_t)));
+        b.cap = need;
+      }
+    }
+  }
+  return B200CRON_OK;
+}
+
 extern "C" int b200cron_unmet_since_dev(b200cron_ctx* ctx, int dev_index, void* stream,
                                         const uint64_t* const masks[6], const int32_t* zone_id,
                                         const int64_t* earliest, int64_t now, int32_t now_nsec, const uint8_t* policy,

@@ -173,13 +173,16 @@ int b200cron_ctx_set_overlap(b200cron_ctx* ctx, int on);
  * next - now (:192).  Gated Crons get ZERO times and missed 0.
  * A call without zone ids is one kernel and uses no scratch.  With zone ids the Crons evaluated in UTC are answered in
  * place, the zoned ones through an index list grouped by zone, and whatever the closed form cannot follow through a
- * second list by the general walk: both lists live in device memory owned by the context (8 bytes per Cron of the
- * largest batch seen, three such buffers per device, allocated when a larger batch first arrives; calls on different
- * streams are kept apart by events). */
+ * second list by the general walk: the lists live in device memory owned by the context (12 bytes per Cron of the
+ * largest batch seen, three such buffers per device, allocated when a larger batch first arrives -- or up front by
+ * b200cron_ctx_reserve_unmet; calls on different streams are kept apart by events). */
 int b200cron_unmet_since(b200cron_ctx* ctx, const uint64_t* const masks[6], const int32_t* zone_id,
                          const int64_t* earliest, int64_t now, int32_t now_nsec, const uint8_t* policy,
                          const uint32_t* active, const uint8_t* flags, const int64_t* deadline, size_t n,
                          int64_t* last, int64_t* next, uint32_t* missed, uint8_t* status, uint8_t* decision);
+/* Optional: allocate that scratch now, for batches of up to max_n Crons per device, so that no later unmet_since call
+ * allocates or frees device memory in the middle of a tick (no counterpart in the reference). */
+int b200cron_ctx_reserve_unmet(b200cron_ctx* ctx, size_t max_n);
 int b200cron_unmet_since_dev(b200cron_ctx* ctx, int dev_index, void* stream, const uint64_t* const masks[6],
                              const int32_t* zone_id, const int64_t* earliest, int64_t now, int32_t now_nsec,
                              const uint8_t* policy, const uint32_t* active, const uint8_t* flags,

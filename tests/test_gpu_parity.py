@@ -804,3 +804,32 @@ def test_unmet_period_clock_class_on_the_device(ctx, names):
             if now < t - back:
                 continue
             _cmp(ctx.unmet_since(base, e, now, zone_id=zz), po.batch_unmet(base, e, now, zone_id=zz, zone_names=names), (t, back, ahead))
+
+
+def test_reserve_unmet_scratch_means_no_allocation_in_the_tick(names):
+    """b200cron_ctx_reserve_unmet sizes the index lists up front: unmet_since_dev calls up to that size then leave the
+    device's free memory untouched (and still answer like the oracle)"""
+    import torch
+    c = api.Context(devices=[0])
+    try:
+        n = 150_001
+        masks = synth.gen_specs(n, seed=33, dense_minutes=0.3)
+        zid = synth.gen_zone_ids(n, len(names), np.arange(1, len(names)), seed=33)
+        now = ts(2026, 3, 29, 12)
+        earliest = now - synth.gen_times(n, 0, 3 * 86400, seed=33)
+        st = torch.cuda.current_stream().cuda_stream
+        dm, dz, de = torch.from_numpy(masks.view(np.int64)).cuda(), torch.from_numpy(zid).cuda(), torch.from_numpy(earliest).cuda()
+        o = dict(last=torch.empty(n, dtype=torch.int64, device="cuda"), next=torch.empty(n, dtype=torch.int64, device="cuda"),
+                 missed=torch.empty(n, dtype=torch.int32, device="cuda"), status=torch.empty(n, dtype=torch.uint8, device="cuda"),
+                 decision=torch.empty(n, dtype=torch.uint8, device="cuda"))
+        c.reserve_unmet(200_000)
+        torch.cuda.synchronize()
+        free0 = torch.cuda.mem_get_info()[0]
+        for _ in range(4):  # more calls than scratch buffers
+            c.unmet_since_dev(dm, de, now, o, zone_id=dz, stream=st)
+        c.sync_check(stream=st)
+        assert torch.cuda.mem_get_info()[0] == free0
+        want = po.batch_unmet(masks, earliest, now, zone_id=zid, zone_names=names)
+        _cmp({k: v.cpu().numpy().view(want[k].dtype) for k, v in o.items()}, want)
+    finally:
+        c.close()
