@@ -315,6 +315,7 @@ cudaError_t launch_unmet(b200cron_ctx* ctx, Device& d, cudaStream_t st, const Un
     unmet_tile_kernel<true, false><<<tiles, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, b.idx, b.count, nullptr, nullptr);
   }
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  if (B200CRON_UNMET_ORDERED_SINGLE && ordered) return cudaEventRecord(b.done, st);  // tuning build: nothing was deferred
   const unsigned hard_max = (unsigned)d.sm_count * B200CRON_UNMET_HARD_MINBLOCKS;
   unmet_hard_kernel<<<grid < hard_max ? grid : hard_max, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, b.idx, b.count);
   if ((e = cudaGetLastError()) != cudaSuccess) return e;

@@ -527,6 +527,9 @@ constexpr int kUnmetEasyRounds = B200CRON_UNMET_EASY_ROUNDS;
 #ifndef B200CRON_UNMET_EASY_MINBLOCKS
 #define B200CRON_UNMET_EASY_MINBLOCKS 8
 #endif
+#ifndef B200CRON_UNMET_ORDERED_SINGLE
+#define B200CRON_UNMET_ORDERED_SINGLE 0
+#endif
 #ifndef B200CRON_UNMET_HARD_MINBLOCKS
 #define B200CRON_UNMET_HARD_MINBLOCKS 12
 #endif
@@ -725,7 +728,13 @@ unmet_ordered_kernel(UnmetArgs a, ZoneTable zt, int* __restrict__ err, uint32_t*
   if (q0 >= cnt) return;  // warp-uniform
   const size_t q = q0 + (threadIdx.x & 31u);
   const bool live = q < cnt;
+#if B200CRON_UNMET_ORDERED_SINGLE
+  // tuning build: the general state machine right here (step emulation out of line), no defer list, no hard kernel --
+  // zone-pure warps either need the emulation in every lane or in none
+  unmet_one<kUnmetSingle>(a, zt, err, live ? (size_t)__ldg(order + q) : 0, live, nullptr, nullptr);
+#else
   unmet_one<kUnmetEasy>(a, zt, err, live ? (size_t)__ldg(order + q) : 0, live, defer_idx, defer_count);
+#endif
 }
 
 // the general state machine over the compact list the easy rounds left behind (grid-stride: the host does not know
