@@ -4,7 +4,7 @@
 N=${1:-1}
 mkdir -p gpurun_out
 for r in $(seq 1 $((N - 1))); do
-  BUSY_SECONDS=${BUSY_SECONDS:-75} python profiles/pern.py $r $N > gpurun_out/pern_n${N}_rank$r.log 2>&1 &
+  BUSY_SECONDS=${BUSY_SECONDS:-50} python profiles/pern.py $r $N > gpurun_out/pern_n${N}_rank$r.log 2>&1 &
 done
 timeout 600 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none \
   -k regex:"next1_kernel|history_prune_kernel" --csv --log-file gpurun_out/ncu_pern_n$N.csv python profiles/pern.py 0 $N \
