@@ -183,6 +183,9 @@ constexpr int kNextTileSpecsZoned = 2048;   // zoned launch: it takes ~7 % of th
 #ifndef B200CRON_NEXTN_UTC_MINBLOCKS
 #define B200CRON_NEXTN_UTC_MINBLOCKS 10
 #endif
+#ifndef B200CRON_NEXTN_ZONED_OUTLINE
+#define B200CRON_NEXTN_ZONED_OUTLINE 0  // 1 (tuning builds): the zoned launch calls the step emulation out of line
+#endif
 #ifndef B200CRON_NEXTN_PAIR
 #define B200CRON_NEXTN_PAIR 1
 #endif
@@ -273,7 +276,7 @@ next_n_tile_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int6
       __syncwarp();  // every lane runs exactly k iterations: re-converge, or lanes on a short path run ahead for good
       int64_t r = kZero;
       if (ok && t != kZero) {
-        t = cronwalk::next_from_t<false, kUtc>(ss, w, t, j > 0);
+        t = cronwalk::next_from_t<(!kUtc && B200CRON_NEXTN_ZONED_OUTLINE), kUtc>(ss, w, t, j > 0);
         if (!kUtc && t != kZero && !ss.every && w.zn > 1 && t >= zt.horizon - kSixYears) { atomicOr(err, kErrRange); ok = false; t = kZero; }
         if (on_period) left = left || t == kZero || t >= nhi;  // the chain left its period: the general walk answers
         r = t == kZero ? kZero : t - shift;
