@@ -17,7 +17,7 @@ for r in rows:
         launches.setdefault((d["ID"], d["Kernel Name"]), {})[d["Metric Name"]] = (float(d["Metric Value"].replace(",", "")), d["Metric Unit"])
 specs = 1_000_000_000 // N
 out = [f"# r2: rank 0's kernels under ncu while all {N} rank(s) run their C5 shard ({specs} specs + 2e7 history segments per GPU)\n",
-       "command: `python -m torch.distributed.run --nproc-per-node N --no-python profiles/ncu_rank0.sh` (rank 0 = `ncu --metrics "
+       "command: `bash profiles/ncu_rank0.sh N` (one plain process per GPU; rank 0 = `ncu --metrics "
        "dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none`; per-launch times under ncu are "
        "serialised and cold: compare the GB/s, not the ms, with bench.py's)\n",
        f"HBM peak (MEASURED_PEAKS.json): {peak} GB/s\n",
