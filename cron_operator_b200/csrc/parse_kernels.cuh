@@ -45,14 +45,12 @@ __device__ inline bool parse_number(const Str& s, uint32_t* out) {
   if (c0 == '+' || c0 == '-') { neg = c0 == '-'; i = 1; }
   if (i == s.n) return false;
   uint64_t v = 0;
-  bool big = false;  // beyond 18 digits: decide int64 overflow exactly
   for (; i < s.n; ++i) {
     const char c = ch(s, i);
     if (c < '0' || c > '9') return false;
     if (v > (0xFFFFFFFFFFFFFFFFULL - 9) / 10) return false;
     v = v * 10 + (uint64_t)(c - '0');
   }
-  (void)big;
   if (neg ? v > (1ULL << 63) : v > (1ULL << 63) - 1) return false;
   if (neg && v > 0) return false;  // "negative number not allowed"
   *out = v > 1000000 ? 1000000u : (uint32_t)v;

@@ -15,3 +15,6 @@ U="python profiles/run_kernel.py unmet 4000000"
 FIVE=1 $U > gpurun_out/plain_u_r2_final.log 2>&1 &&
 FIVE=1 ncu --set full --clock-control none --import-source on -k regex:unmet_tile -s 2 -c 1 -f -o gpurun_out/prof_unmet_tile_r2_final $U > gpurun_out/ncu_ut_r2_final.log 2>&1
 ls -la gpurun_out/*r2_final*
+{
+for v in "" $(ls cron_operator_b200/csrc/variants/lib_o_*.so 2>/dev/null); do echo "== nextn ${v:-default}"; B200CRON_LIB=$v python profiles/run_kernel.py nextn 8000000 5; done
+} 2>&1 | tee gpurun_out/ab_r2_final.log
