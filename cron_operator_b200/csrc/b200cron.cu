@@ -138,15 +138,13 @@ const T* dev_alias(const T* p) {  // p is known to be pinned (is_pinned_host) or
 template <typename T>
 T* dev_alias(T* p) { return const_cast<T*>(dev_alias(static_cast<const T*>(p))); }
 
-bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+[[maybe_unused]] bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
-// B200CRON_NEXTN_SPLIT (tuning builds): 1 = k > 1 launches walk class-pure warps (next_n_tile_kernel, one launch per
-// class); 0 = one launch of next_n_kernel over the specs in input order.
-#ifndef B200CRON_NEXTN_SPLIT
-#define B200CRON_NEXTN_SPLIT 1
-#endif
+// B200CRON_NEXTN_SPLIT (kernels.cuh): 1 = k > 1 launches walk class-pure warps (next_n_tile_kernel, one launch per
+// class); 0 (tuning builds) = one launch of next_n_kernel over the specs in input order.
 
 // ---- launches -------------------------------------------------------------------------------------------------
+#if !B200CRON_NEXTN_SPLIT
 template <int KT>
 cudaError_t launch_next_kt(bool vec, unsigned grid, size_t smem, cudaStream_t st, const MaskPlanes& m,
                            const int32_t* zone, const int64_t* from, size_t n, int k, int64_t* out,
@@ -162,6 +160,7 @@ cudaError_t launch_next_kt(bool vec, unsigned grid, size_t smem, cudaStream_t st
   }
   return cudaGetLastError();
 }
+#endif
 
 #ifndef B200CRON_NEXT1_FIVE
 #define B200CRON_NEXT1_FIVE 1  // 0 (tuning builds): launches without a seconds plane use the general instantiation
@@ -181,10 +180,14 @@ cudaError_t launch_next_kt(bool vec, unsigned grid, size_t smem, cudaStream_t st
 cudaError_t launch_next(b200cron_ctx* ctx, const Device& d, cudaStream_t st, const MaskPlanes& m, const int32_t* zone,
                         const int64_t* from, size_t n, int k, int64_t* out, bool device_resident) {
   if (n == 0) return cudaSuccess;
+#if B200CRON_NEXT1_RING || !B200CRON_NEXTN_SPLIT  // only the tuning-build kernels use 128-bit accesses
   bool vec = aligned16(from) && aligned16(out) && (!zone || (reinterpret_cast<uintptr_t>(zone) & 7u) == 0);
   for (int p = 0; p < 6; ++p) vec = vec && (m.p[p] == nullptr || aligned16(m.p[p]));
+#endif
+#if !B200CRON_NEXTN_SPLIT
   const unsigned grid = (unsigned)((n + kNextTile - 1) / kNextTile);
   const size_t smem = (k == 1 || !kNextStage) ? 0 : (size_t)kNextTile * k * sizeof(int64_t);
+#endif
   ctx->launches.fetch_add(1, std::memory_order_relaxed);
   if (k == 1) {  // one spec per lane (finer waves than next_n_kernel's two)
     if (n > 0xffffffffULL) return cudaErrorInvalidValue;  // next1_kernel indexes with 32 bits (4G specs = 240 GB of inputs)
@@ -235,7 +238,7 @@ cudaError_t launch_next(b200cron_ctx* ctx, const Device& d, cudaStream_t st, con
     if (k == 16) return go(std::integral_constant<int, 16>{});
     return go(std::integral_constant<int, 0>{});
   }
-#endif
+#else
   switch (k) {
     case 2: return launch_next_kt<2>(vec, grid, smem, st, m, zone, from, n, k, out, d.zt, d.d_err);
     case 4: return launch_next_kt<4>(vec, grid, smem, st, m, zone, from, n, k, out, d.zt, d.d_err);
@@ -244,6 +247,7 @@ cudaError_t launch_next(b200cron_ctx* ctx, const Device& d, cudaStream_t st, con
     case 32: return launch_next_kt<32>(vec, grid, smem, st, m, zone, from, n, k, out, d.zt, d.d_err);
     default: return launch_next_kt<0>(vec, grid, smem, st, m, zone, from, n, k, out, d.zt, d.d_err);
   }
+#endif
 }
 
 // B200CRON_UNMET_PLAN (tuning builds, profiles/build_variants.sh): 0 = the tile kernel handles both classes in input
@@ -310,9 +314,11 @@ cudaError_t launch_unmet(b200cron_ctx* ctx, Device& d, cudaStream_t st, const Un
     // the scatter advanced cursor[z] to the end of zone z's range; cursor[nz] (the total) is untouched
     unmet_ordered_kernel<<<grid, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, b.idx, b.count, order, cursor + nz);
   } else {
+#if B200CRON_UNMET_PLAN != 1
     if ((e = cudaMemsetAsync(b.count, 0, sizeof(uint32_t), st)) != cudaSuccess) return e;
     ctx->launches.fetch_add(2, std::memory_order_relaxed);
     unmet_tile_kernel<true, false><<<tiles, kUnmetThreads, 0, st>>>(a, d.zt, d.d_err, b.idx, b.count, nullptr, nullptr);
+#endif
   }
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
   if (B200CRON_UNMET_ORDERED_SINGLE && ordered) return cudaEventRecord(b.done, st);  // tuning build: nothing was deferred

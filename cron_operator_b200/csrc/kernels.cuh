@@ -1,6 +1,7 @@
-// kernels.cuh -- sm_100a kernels of libb200cron.so.  All are HBM-bound integer kernels (no contraction, so no
-// tensor cores): SoA mask planes are read with coalesced 128-bit loads, one lane walks one spec (cron_walk.cuh),
-// and outputs leave through shared-memory staging so that every warp writes full 128-byte lines.
+// kernels.cuh -- sm_100a kernels of libb200cron.so.  Integer kernels bound by the scope table to the HBM line (no
+// contraction, so no tensor cores): SoA mask planes are read with coalesced loads, one lane walks one spec
+// (cron_walk.cuh), and warps are made class-pure (UTC / one zone period's clock / general zoned) by ballot compaction
+// before the walk, so that the short instantiations of the walk run in dense warps.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -36,7 +37,13 @@ __device__ __forceinline__ bool bind_checked(Walk& w, const ZoneTable& zt, int32
   return true;
 }
 
+#ifndef B200CRON_NEXTN_SPLIT
+#define B200CRON_NEXTN_SPLIT 1  // 0 (tuning builds): k > 1 launches use next_n_kernel over the specs in input order
+#endif
+
+#if !B200CRON_NEXTN_SPLIT
 // -------------------------------------------------------------------------------------------------------------
+// (tuning builds only: round 1's kernel, kept as the A/B baseline of next_n_tile_kernel)
 // next_n: out[i*k + j] = (j+1)-th chained Next() after from[i]              (spec.go Next; cron_controller.go:405,409,436)
 //
 // Layout: each warp owns 64 consecutive specs.  Lane l loads specs (2l, 2l+1) of that tile from each of the 6
@@ -165,8 +172,11 @@ next_n_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* 
 }
 
 
+#endif  // !B200CRON_NEXTN_SPLIT
+
 // -------------------------------------------------------------------------------------------------------------
-// next_n over class-pure warps (k > 1 with zone ids).  In input order half of a C3 warp's lanes are UTC and ride
+// next_n: out[i*k + j] = (j+1)-th chained Next() after from[i]              (spec.go Next; cron_controller.go:405,409,436)
+// over class-pure warps (k > 1).  In input order half of a C3 warp's lanes are UTC and ride
 // through the zoned instruction stream (zone prerequisites, period lookups, the step emulation), and the kernel sits at
 // 80 registers for everybody.  Here a CTA takes a tile of kNextTileSpecs consecutive specs, deals the indices of ONE
 // class -- evaluated in UTC (kUtc) or in a zone -- into shared memory with a ballot compaction and walks only those, in
