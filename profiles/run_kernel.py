@@ -63,6 +63,24 @@ if which == "unmet":
              decision=torch.empty(n, dtype=torch.uint8, device="cuda"))
     five = bool(os.environ.get("FIVE"))  # FIVE=1: no seconds plane (5-field schedules)
     fn = lambda: ctx.unmet_since_dev(dm, de, now, o, 0, dp, da, dfl, ddl, dz, stream=st, five_field=five)  # noqa: E731
+elif which == "list":
+    # the capped list of missed runs (cap 100) on the C4 shape: offsets, then the warp-cooperative emission
+    m = synth.gen_specs(n, seed=41, dense_minutes=0.5)
+    z = synth.gen_zone_ids(n, len(names), dst, seed=41)
+    now = synth.ts(2026, 3, 29, 12)
+    e = now - 30 * 86400 + synth.gen_times(n, -86400, 86400, seed=41)
+    dm, dz, de = t(m.view(np.int64)), t(z), t(e)
+    o = dict(last=torch.empty(n, dtype=torch.int64, device="cuda"), next=torch.empty(n, dtype=torch.int64, device="cuda"),
+             missed=torch.empty(n, dtype=torch.int32, device="cuda"), status=torch.empty(n, dtype=torch.uint8, device="cuda"),
+             decision=torch.empty(n, dtype=torch.uint8, device="cuda"))
+    ctx.unmet_since_dev(dm, de, now, o, zone_id=dz, stream=st)
+    off = torch.empty(n + 1, dtype=torch.int64, device="cuda")
+    ctx.unmet_list_offsets_dev(o["missed"], o["decision"], off, 100, stream=st)
+    ctx.sync_check(stream=st)
+    total = int(off[-1].item())
+    lst = torch.empty(total, dtype=torch.int64, device="cuda")
+    print("list entries", total, "bytes", total * 8)
+    fn = lambda: ctx.unmet_list_emit_dev(dm, de, off, lst, dz, stream=st)  # noqa: E731
 elif which == "nextn":
     m = synth.gen_specs(n, seed=3, with_seconds=True)
     z = synth.gen_zone_ids(n, len(names), dst, seed=3)
@@ -92,6 +110,8 @@ for _ in range(reps):
 extra = ""
 if which == "nextn":  # variants must agree: a cheap fingerprint of the whole output
     extra = " checksum %d" % int((o ^ (o >> 17)).sum().item())
+if which == "list":
+    extra = " checksum %d  GB/s out %.0f" % (int((lst ^ (lst >> 17)).sum().item()), total * 8 / (best * 1e-3) / 1e9)
 if which == "unmet":
     extra = " checksum %d" % int(sum((v.to(torch.int64) * (j + 3)).sum().item() for j, v in enumerate(o.values())) & (2**63 - 1))
 print(which, n, "ms", best, extra)
