@@ -190,7 +190,7 @@ cudaError_t launch_next(b200cron_ctx* ctx, const Device& d, cudaStream_t st, con
 #endif
   ctx->launches.fetch_add(1, std::memory_order_relaxed);
   if (k == 1) {  // one spec per lane (finer waves than next_n_kernel's two)
-    if (n > 0xffffffffULL) return cudaErrorInvalidValue;  // next1_kernel indexes with 32 bits (4G specs = 240 GB of inputs)
+    if (n > 0xffffff00ULL) return cudaErrorInvalidValue;  // next1_kernel indexes with 32 bits (4G specs = 240 GB of inputs)
     const unsigned g1 = (unsigned)((n + kNext1Threads - 1) / kNext1Threads);
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(g1);
