@@ -138,6 +138,50 @@ class Engine {
 
   b200cron_ctx* handle() const { return ctx_; }
 
+  // A resident set of schedules (b200cron_specset_*): a SpecSchedule is immutable once ParseStandard has built it
+  // (cron_controller.go:392), so a host that ticks the same Crons again and again parks their masks on the GPU once
+  // and then moves only the per-tick arrays.  Destroy it before the Engine.
+  class SpecSet {
+   public:
+    SpecSet(Engine& e, const std::vector<Schedule>& specs) : e_(e), n_(specs.size()) {
+      Planes p(e, specs);
+      e.Check(b200cron_specset_create(e.ctx_, p.ptr, p.zone.data(), n_, &set_));
+    }
+    ~SpecSet() { b200cron_specset_destroy(set_); }
+    SpecSet(const SpecSet&) = delete;
+    SpecSet& operator=(const SpecSet&) = delete;
+    size_t size() const { return n_; }
+    // the Cron at `index` got a new schedule (its CR was edited)
+    void Update(size_t index, const Schedule& s) {
+      Planes p(e_, {s});
+      e_.Check(b200cron_specset_update(set_, index, 1, p.ptr, p.zone.data()));
+    }
+    std::vector<int64_t> NextN(const std::vector<int64_t>& from, int k) {
+      std::vector<int64_t> out(n_ * (size_t)k);
+      e_.Check(b200cron_next_n_set(e_.ctx_, set_, from.data(), k, out.data()));
+      return out;
+    }
+    std::vector<Unmet> UnmetSince(const std::vector<int64_t>& earliest, int64_t now, const std::vector<uint8_t>& policy = {},
+                                  const std::vector<uint32_t>& active = {}, const std::vector<uint8_t>& flags = {},
+                                  const std::vector<int64_t>& deadline = {}, int32_t now_nsec = 0) {
+      std::vector<int64_t> last(n_), next(n_);
+      std::vector<uint32_t> missed(n_);
+      std::vector<uint8_t> status(n_), decision(n_);
+      e_.Check(b200cron_unmet_since_set(e_.ctx_, set_, earliest.data(), now, now_nsec,
+                                        policy.empty() ? nullptr : policy.data(), active.empty() ? nullptr : active.data(),
+                                        flags.empty() ? nullptr : flags.data(), deadline.empty() ? nullptr : deadline.data(),
+                                        last.data(), next.data(), missed.data(), status.data(), decision.data()));
+      std::vector<Unmet> out(n_);
+      for (size_t i = 0; i < n_; ++i) out[i] = Unmet{last[i], next[i], missed[i], status[i], decision[i]};
+      return out;
+    }
+
+   private:
+    Engine& e_;
+    size_t n_;
+    b200cron_specset* set_ = nullptr;
+  };
+
  private:
   struct Planes {  // SoA planes + zone ids of a batch of schedules
     std::vector<uint64_t> m[6];

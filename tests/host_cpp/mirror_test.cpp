@@ -67,6 +67,19 @@ static int gpu() {
   std::printf("unmet");
   for (const Unmet& u : um) std::printf(" %" PRId64 " %" PRId64 " %u %u %u", u.last, u.next, u.missed, (unsigned)u.status, (unsigned)u.decision);
   std::printf("\n");
+  {  // the same two calls through a resident set, before and after one Cron's schedule is edited
+    Engine::SpecSet set(e, specs);
+    const auto sn = set.NextN({kNow, 1772935200, kNow, kNow}, 3);
+    const auto su = set.UnmetSince({kNow - 3600, kNow - 5 * 86400, kNow - 86400, kNow + 10}, kNow, {0, 1, 2, 0}, {0, 2, 1, 0});
+    bool same = sn == nn && su.size() == um.size();
+    for (size_t i = 0; same && i < su.size(); ++i)
+      same = su[i].last == um[i].last && su[i].next == um[i].next && su[i].missed == um[i].missed &&
+             su[i].status == um[i].status && su[i].decision == um[i].decision;
+    set.Update(2, specs[0]);
+    const auto sn2 = set.NextN({kNow, 1772935200, kNow, kNow}, 3);
+    same = same && sn2[6] == nn[0] && sn2[7] == nn[1] && sn2[8] == nn[2] && sn2[0] == nn[0] && sn2[9] == nn[9];
+    std::printf("specset %s\n", same ? "same" : "DIFFERENT");
+  }
   std::vector<uint32_t> perm;
   std::vector<uint8_t> keep;
   e.HistoryPrune({0, 5, 5, 8}, {5, 3, 9, 3, 7, 2, 2, 1}, {3, 1, -1}, &perm, &keep);

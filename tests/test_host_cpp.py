@@ -58,6 +58,7 @@ def test_reference_cases_and_batches_through_the_cpp_mirror():
     assert out["k2"] == 'unschedulable cron "0 0 30 2 *"'                  # K2, :411
     assert out["k3"].split() == [str(NOW), str(NOW + 60)]                  # K3
     assert out["every"].split() == [str(NOW - 20), str(NOW + 90)]
+    assert out["specset"] == "same"                                        # Engine::SpecSet == the host-pointer calls
     texts = ["*/5 * * * *", "TZ=America/New_York 30 2 * * *", "0 0 29 2 *", "15 3 * * 0"]
     specs = [api.ParseStandard(t) for t in texts]
     ctx = api.Context()
