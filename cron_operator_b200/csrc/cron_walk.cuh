@@ -29,9 +29,6 @@
 #define CW_LDG(p) (*(p))
 #endif
 
-#ifndef B200CRON_UTC_CHAIN_SHORTCUT
-#define B200CRON_UTC_CHAIN_SHORTCUT 1  // 0 (tuning builds): chained UTC calls always go through fast_next's prologue
-#endif
 #ifndef CW_TRACE
 #define CW_TRACE(tag, w)
 #endif
@@ -778,17 +775,6 @@ template <bool kUtcOnly = false>
 CW_HD bool next_try(const Spec& s, Walk& w, int64_t t, bool resident, int64_t* out) {
   CW_COUNT(next);
   if (s.never) { *out = s.every ? t + (int64_t)s.second : kZero; return true; }  // constantdelay.go Next: t.Add(Delay)
-  if (kUtcOnly && B200CRON_UTC_CHAIN_SHORTCUT && resident && w.today_ok) {
-    // Chained call on one clock, on a day already known to match: if the day has a later matching time, that is the
-    // answer -- exactly what fast_next would find after its prologue (same result, same state), without the prologue.
-    const int32_t tod = next_tod_ge(s, w.sod + 1);
-    if (tod >= 0) {
-      w.t += tod - w.sod;
-      w.sod = tod;
-      *out = w.t;
-      return true;
-    }
-  }
   const int64_t t1 = t + 1;
   if (resident && (kUtcOnly || t1 < w.pe) && w.sod + 1 < 86400) {
     w.t = t1;
