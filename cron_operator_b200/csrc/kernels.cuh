@@ -362,7 +362,8 @@ next1_kernel(MaskPlanes m, const int32_t* __restrict__ zone_id, const int64_t* _
 }
 
 // -------------------------------------------------------------------------------------------------------------
-// next1 with persistent warps and an asynchronous input ring (the default for k == 1 on device-resident inputs).
+// next1 with persistent warps and an asynchronous input ring.  TUNING BUILD ONLY (-DB200CRON_NEXT1_RING=1): measured
+// slower than next1_kernel (18.8 vs 13.7 us per 1M specs), kept as the record of that experiment.
 //
 // next1_kernel gives every warp one tile: issue seven loads, wait a DRAM round trip, walk, store, exit -- the wait is
 // the kernel's top stall, and a 1M-spec launch ends in a ragged last wave.  Here the grid is sized to the machine

@@ -1,5 +1,5 @@
 """Heavy randomized stress of the kernels' walk source (host build) vs the oracle.  Not collected by pytest (no
-test_ prefix); run by hand:  python tests/stress_walk.py [rounds]"""
+test_ prefix); run by hand:  python tests/stress_walk.py [rounds [seed]]  (seed 0 = the sequence the round logs quote)"""
 import sys
 import time
 
@@ -29,13 +29,13 @@ def near_transition_times(rng, zid, lo, hi, spread):
     return out
 
 
-def main(rounds):
-    rng = np.random.default_rng(12345)
+def main(rounds, salt=0):
+    rng = np.random.default_rng(12345 + salt)
     tot = 0
     t0 = time.time()
     for r in range(rounds):
         n = 40000
-        seed = 1000 + r
+        seed = 1000 + r + 100003 * salt
         ws = bool(r % 2)
         masks = synth.gen_specs(n, seed=seed, with_seconds=ws, dense_minutes=0.3 if r % 3 == 0 else 0.0)
         zid = rng.integers(1, len(NAMES), n).astype(np.int32)
@@ -90,4 +90,4 @@ def main(rounds):
 
 
 if __name__ == "__main__":
-    sys.exit(main(int(sys.argv[1]) if len(sys.argv) > 1 else 8))
+    sys.exit(main(int(sys.argv[1]) if len(sys.argv) > 1 else 8, int(sys.argv[2]) if len(sys.argv) > 2 else 0))
