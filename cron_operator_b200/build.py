@@ -9,7 +9,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(CSRC, "libb200cron.so")
 SOURCES = ["b200cron.cu", "parse.cpp", "zone_table.cpp"]
-HEADERS = ["kernels.cuh", "cron_walk.cuh", "unmet_walk.cuh", "zone_table.h", os.path.join("..", "..", "include", "b200cron.h")]
+# every header next to the sources (a hand-kept list once missed parse_kernels.cuh and synth_kernels.cuh) + the ABI
+HEADERS = sorted(f for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))) + [os.path.join("..", "..", "include", "b200cron.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
               "-Xcompiler", "-Wall", "-shared"]
 

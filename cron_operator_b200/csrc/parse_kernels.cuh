@@ -8,9 +8,20 @@
 // Zone names cannot be resolved on the device: the span of the name inside the spec is returned and the host maps
 // it to a zone id.  "@every <duration>" with plain h/m/s terms is parsed here; other durations are flagged (status 2)
 // and left to the host.
+//
+// The grammar lives in parse_one(), which also compiles as plain C++ (PK_HD / PK_LDG below): tests/host_shim builds it
+// with g++ so the CPU suite can fuzz the very source the kernel runs against the oracle's parser.
 #pragma once
-#include <cuda_runtime.h>
 #include <stdint.h>
+#ifdef __CUDACC__
+#include <cuda_runtime.h>
+#define PK_HD __device__
+#define PK_LDG(p) __ldg(p)
+#else
+#define PK_HD
+#define PK_LDG(p) (*(p))
+#define __forceinline__ inline
+#endif
 
 namespace b200cron {
 
@@ -20,15 +31,15 @@ struct Str {
   const char* p;
   int n;
 };
-__device__ __forceinline__ char ch(const Str& s, int i) { return __ldg(s.p + i); }
-__device__ __forceinline__ bool is_space(char c) { return c == ' ' || c == '\t' || c == '\n' || c == '\v' || c == '\f' || c == '\r'; }
-__device__ __forceinline__ bool equals(const Str& s, const char* lit, int n) {
+PK_HD __forceinline__ char ch(const Str& s, int i) { return PK_LDG(s.p + i); }
+PK_HD __forceinline__ bool is_space(char c) { return c == ' ' || c == '\t' || c == '\n' || c == '\v' || c == '\f' || c == '\r'; }
+PK_HD __forceinline__ bool equals(const Str& s, const char* lit, int n) {
   if (s.n != n) return false;
   for (int i = 0; i < n; ++i)
     if (ch(s, i) != lit[i]) return false;
   return true;
 }
-__device__ __forceinline__ bool starts_with(const Str& s, const char* lit, int n) {
+PK_HD __forceinline__ bool starts_with(const Str& s, const char* lit, int n) {
   if (s.n < n) return false;
   for (int i = 0; i < n; ++i)
     if (ch(s, i) != lit[i]) return false;
@@ -37,7 +48,7 @@ __device__ __forceinline__ bool starts_with(const Str& s, const char* lit, int n
 
 // strconv.Atoi + mustParseInt: optional sign, digits, int64 range, negative values rejected.  Values are capped at
 // 1e6 (anything that large fails the range checks that follow).
-__device__ inline bool parse_number(const Str& s, uint32_t* out) {
+PK_HD inline bool parse_number(const Str& s, uint32_t* out) {
   if (s.n == 0) return false;
   int i = 0;
   bool neg = false;
@@ -57,10 +68,10 @@ __device__ inline bool parse_number(const Str& s, uint32_t* out) {
   return true;
 }
 
-__device__ __forceinline__ char lower(char c) { return (c >= 'A' && c <= 'Z') ? (char)(c + 32) : c; }
+PK_HD __forceinline__ char lower(char c) { return (c >= 'A' && c <= 'Z') ? (char)(c + 32) : c; }
 
 // parseIntOrName; names: 0 none, 1 months (jan..dec -> 1..12), 2 weekdays (sun..sat -> 0..6)
-__device__ inline bool parse_number_or_name(const Str& s, int names, uint32_t* out) {
+PK_HD inline bool parse_number_or_name(const Str& s, int names, uint32_t* out) {
   if (names && s.n == 3) {
     const char a = lower(ch(s, 0)), b = lower(ch(s, 1)), c = lower(ch(s, 2));
     const char* tab = names == 1 ? "janfebmaraprmayjunjulaugsepoctnovdec" : "sunmontuewedthufrisat";
@@ -75,7 +86,7 @@ __device__ inline bool parse_number_or_name(const Str& s, int names, uint32_t* o
 }
 
 // getRange: one `lo[-hi][/step]` term -> bits (with the star bit); false on any upstream error
-__device__ inline bool parse_term(const Str& e, uint32_t lo_b, uint32_t hi_b, int names, uint64_t* bits) {
+PK_HD inline bool parse_term(const Str& e, uint32_t lo_b, uint32_t hi_b, int names, uint64_t* bits) {
   int slash = -1, nslash = 0;
   for (int i = 0; i < e.n; ++i)
     if (ch(e, i) == '/') { if (nslash == 0) slash = i; ++nslash; }
@@ -111,7 +122,7 @@ __device__ inline bool parse_term(const Str& e, uint32_t lo_b, uint32_t hi_b, in
 }
 
 // getField: comma list, empty pieces dropped
-__device__ inline bool parse_field(const Str& f, uint32_t lo_b, uint32_t hi_b, int names, uint64_t* bits) {
+PK_HD inline bool parse_field(const Str& f, uint32_t lo_b, uint32_t hi_b, int names, uint64_t* bits) {
   uint64_t acc = 0;
   int st = 0;
   for (int i = 0; i <= f.n; ++i) {
@@ -132,14 +143,11 @@ struct ParseOut {
   uint64_t* p[6];
 };
 
-__global__ void __launch_bounds__(128)
-parse_batch_kernel(const char* __restrict__ text, const uint64_t* __restrict__ text_off, size_t n, int with_seconds,
-                   ParseOut out, uint8_t* __restrict__ status, uint32_t* __restrict__ tz_off, uint32_t* __restrict__ tz_len) {
-  const size_t i = (size_t)blockIdx.x * 128 + threadIdx.x;
-  if (i >= n) return;
-  const uint64_t a = __ldg(text_off + i), b = __ldg(text_off + i + 1);
-  Str s{text + a, (int)(b - a)};
-  uint64_t m[6] = {0, 0, 0, 0, 0, 0};
+// One spec: masks (zeroed on error), status, and the span of the zone name inside the text (relative to its start;
+// offset 0xFFFFFFFF = "TZ= ...", the empty name, which LoadLocation reads as UTC).
+PK_HD inline uint8_t parse_one(Str s, int with_seconds, uint64_t m[6], uint32_t* zo_out, uint32_t* zl_out) {
+#pragma unroll
+  for (int p = 0; p < 6; ++p) m[p] = 0;
   uint8_t st = kParseError;
   uint32_t zo = 0, zl = 0;
   const uint64_t kStar = 1ULL << 63;
@@ -226,11 +234,27 @@ parse_batch_kernel(const char* __restrict__ text, const uint64_t* __restrict__ t
 #pragma unroll
     for (int p = 0; p < 6; ++p) m[p] = 0;
   }
+  *zo_out = zo;
+  *zl_out = zl;
+  return st;
+}
+
+#ifdef __CUDACC__
+__global__ void __launch_bounds__(128)
+parse_batch_kernel(const char* __restrict__ text, const uint64_t* __restrict__ text_off, size_t n, int with_seconds,
+                   ParseOut out, uint8_t* __restrict__ status, uint32_t* __restrict__ tz_off, uint32_t* __restrict__ tz_len) {
+  const size_t i = (size_t)blockIdx.x * 128 + threadIdx.x;
+  if (i >= n) return;
+  const uint64_t a = __ldg(text_off + i), b = __ldg(text_off + i + 1);
+  uint64_t m[6];
+  uint32_t zo, zl;
+  const uint8_t st = parse_one(Str{text + a, (int)(b - a)}, with_seconds, m, &zo, &zl);
 #pragma unroll
   for (int p = 0; p < 6; ++p) out.p[p][i] = m[p];
   status[i] = st;
   tz_off[i] = zo;
   tz_len[i] = zl;
 }
+#endif
 
 }  // namespace b200cron

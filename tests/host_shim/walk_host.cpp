@@ -8,6 +8,7 @@
 #include <string>
 
 #include "cron_walk.cuh"
+#include "parse_kernels.cuh"
 #include "unmet_walk.cuh"
 #include "zone_table.h"
 
@@ -153,6 +154,18 @@ void shim_unmet_two_phase(void* table, const uint64_t* const masks[6], const int
     }
     rounds[i] = (uint8_t)r; deferred[i] = defer ? 1 : 0;
     last[i] = st.o.last; next[i] = st.o.next; missed[i] = st.o.missed; status[i] = st.o.status; decision[i] = st.o.decision;
+  }
+}
+
+// parse_batch_kernel's per-spec body (parse_kernels.cuh parse_one) over a batch laid out as the ABI takes it:
+// concatenated text + n+1 offsets; tz_off relative to each spec's start, as the kernel writes it
+void shim_parse_batch(const char* text, const uint64_t* text_off, size_t n, int with_seconds, uint64_t* const masks[6],
+                      uint8_t* status, uint32_t* tz_off, uint32_t* tz_len) {
+  for (size_t i = 0; i < n; ++i) {
+    uint64_t m[6];
+    status[i] = b200cron::parse_one(b200cron::Str{text + text_off[i], (int)(text_off[i + 1] - text_off[i])}, with_seconds, m,
+                                    &tz_off[i], &tz_len[i]);
+    for (int p = 0; p < 6; ++p) masks[p][i] = m[p];
   }
 }
 

@@ -22,7 +22,7 @@ def lib():
         tag = "".join(c if c.isalnum() else "_" for c in "".join(extra))
         so = os.path.join(HERE, "host_shim", f"libwalk_host{tag}.so")
         srcs = [os.path.join(HERE, "host_shim", "walk_host.cpp"), os.path.join(CSRC, "zone_table.cpp")]
-        deps = srcs + [os.path.join(CSRC, f) for f in ("cron_walk.cuh", "unmet_walk.cuh", "zone_table.h")]
+        deps = srcs + [os.path.join(CSRC, f) for f in ("cron_walk.cuh", "unmet_walk.cuh", "parse_kernels.cuh", "zone_table.h")]
         if not os.path.exists(so) or any(os.path.getmtime(d) > os.path.getmtime(so) for d in deps):
             subprocess.check_call(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-I" + CSRC] + extra + ["-o", so] + srcs)
         L = C.CDLL(so)
@@ -42,6 +42,7 @@ def lib():
         L.shim_set_klass_out.argtypes = [C.c_void_p]
         L.shim_unmet_two_phase.argtypes = ([C.c_void_p] * 4 + [C.c_int64, C.c_int32] + [C.c_void_p] * 4 +
                                            [C.c_size_t, C.c_int] + [C.c_void_p] * 7)
+        L.shim_parse_batch.argtypes = [C.c_char_p, C.c_void_p, C.c_size_t, C.c_int] + [C.c_void_p] * 4
         _LIB = L
     return _LIB
 
@@ -125,3 +126,17 @@ def unmet_two_phase(masks, earliest, now, easy_rounds, now_nsec=0, policy=None, 
                                missed.ctypes.data, status.ctypes.data, decision.ctypes.data, rounds.ctypes.data,
                                deferred.ctypes.data)
     return dict(last=last, next=nxt, missed=missed, status=status, decision=decision, rounds=rounds, deferred=deferred)
+
+
+def parse_batch(texts, with_seconds=False):
+    """the device parser's per-spec source (parse_kernels.cuh parse_one) on the host: masks (6, n), status, tz_off, tz_len"""
+    blobs = [t if isinstance(t, bytes) else t.encode("utf-8", errors="surrogateescape") for t in texts]
+    n = len(blobs)
+    off = np.zeros(n + 1, dtype=np.uint64)
+    off[1:] = np.cumsum([len(b) for b in blobs])
+    masks = np.zeros((6, n), dtype=np.uint64)
+    status = np.empty(n, np.uint8)
+    tz_off, tz_len = np.empty(n, np.uint32), np.empty(n, np.uint32)
+    lib().shim_parse_batch(b"".join(blobs), off.ctypes.data, n, int(with_seconds), _planes(masks), status.ctypes.data,
+                           tz_off.ctypes.data, tz_len.ctypes.data)
+    return masks, status, tz_off, tz_len
