@@ -20,7 +20,9 @@
 #else
 #define PK_HD
 #define PK_LDG(p) (*(p))
+#ifndef __forceinline__
 #define __forceinline__ inline
+#endif
 #endif
 
 namespace b200cron {
