@@ -23,6 +23,20 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(L, n), f"{n} declared in include/b200cron.h but not exported"
 
 
+def test_bindings_and_docs_name_only_declared_symbols():
+    """the cgo shim (go/b200cron, never compiled here), the C++ mirror and the documents may only name entry points
+    that include/b200cron.h declares -- keeps the uncompiled Go source and INTEGRATION.md from drifting off the ABI"""
+    import glob
+    hdr = open(os.path.join(ROOT, "include", "b200cron.h")).read()
+    declared = set(re.findall(r"\b(b200cron_[a-z_0-9]+)\s*\(", hdr)) | {"b200cron_ctx", "b200cron_spec", "b200cron_specset"}
+    files = glob.glob(os.path.join(ROOT, "go", "b200cron", "*.go")) + [
+        os.path.join(ROOT, f) for f in ("INTEGRATION.md", "README.md", "DESIGN.md", os.path.join("include", "b200cron.hpp"))]
+    assert len(files) >= 6
+    for f in files:
+        used = {u for u in re.findall(r"\b(b200cron_[a-z0-9_]+)\b", open(f).read()) if not u.endswith("_")}
+        assert not (used - declared), (f, sorted(used - declared))
+
+
 def test_no_cpu_fallback_without_gpu():
     import torch
     if torch.cuda.is_available():
