@@ -130,3 +130,48 @@ def test_upstream_literal_behaviour_at_odd_transitions(zone, text, frm, want):
     m = np.ascontiguousarray(np.array([spec.tuple()], dtype=np.uint64).T)
     got = shim.next_n(m, np.array([t], np.int64), 1, np.array([NAMES.index(zone)], np.int32))
     assert int(got[0, 0]) == w
+
+
+def test_get_next_schedule_matches_an_algorithm_free_scan():
+    """getNextSchedule (internal/controller/cron_controller.go:389-437): lastMissed, Next(now) and the number of missed
+    runs, against a scan that simply lists the matching minutes of (earliest, now] -- UTC and windows holding an
+    ordinary DST transition; oracle and the kernels' classed unmet machine (host build)"""
+    cands = _ordinary_transitions()
+    rng = random.Random(405)
+    parsed = {text: po.parse_standard(text)[0] for text in SPECS}
+    n = 400
+    zid, texts, earliest = [], [], []
+    # one `now` per call (as one reconcile tick has): take a transition, then Crons in zones that switch near it
+    zi0, tr0 = rng.choice([c for c in cands if ts(2015) < c[1] < ts(2030)])
+    now = tr0 + rng.randrange(3600, 2 * 86400)
+    near = [c for c in cands if abs(c[1] - tr0) < 3 * 86400] or [(zi0, tr0)]
+    for i in range(n):
+        zid.append(0 if i % 4 == 0 else rng.choice(near)[0])
+        texts.append(rng.choice(SPECS))
+        earliest.append(now - rng.randrange(0, 4 * 86400))
+    masks = np.ascontiguousarray(np.array([parsed[t].tuple() for t in texts], dtype=np.uint64).T)
+    zid = np.array(zid, dtype=np.int32)
+    earliest = np.array(earliest, dtype=np.int64)
+    want = po.batch_unmet(masks, earliest, now, zone_id=zid, zone_names=NAMES)
+    got = shim.unmet(masks, earliest, now, zone_id=zid)
+    for key in ("last", "next", "missed", "status", "decision"):
+        assert np.array_equal(got[key], want[key]), key
+    checked = 0
+    for i in range(n):
+        try:
+            z = dt.timezone.utc if zid[i] == 0 else zoneinfo.ZoneInfo(NAMES[zid[i]])
+        except Exception:
+            continue
+        m = parsed[texts[i]].tuple()
+        fires = []
+        cur = (int(earliest[i]) // 60 + 1) * 60
+        while cur <= now:
+            if _matches(m, dt.datetime.fromtimestamp(cur, z)):
+                fires.append(cur)
+            cur += 60
+        nxt = _first_match_by_scan(m, z, now, now + 40 * 86400)
+        assert int(want["missed"][i]) == len(fires), (NAMES[zid[i]], texts[i], int(earliest[i]), now)
+        assert int(want["last"][i]) == (fires[-1] if fires else po.ZERO)
+        assert nxt is not None and int(want["next"][i]) == nxt
+        checked += 1
+    assert checked > 350 and int(want["missed"].max()) > 100  # the TooManyMissedTimes range is in the sample
