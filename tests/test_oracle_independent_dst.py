@@ -9,7 +9,7 @@ instant by scanning minute by minute with python's zoneinfo (an independent TZif
 of every zone between 1980 and 2037.
 
 Transitions that touch local midnight, shift by 30/45 minutes or happen off the hour are different: there upstream's
-loops (no re-check of the hour after the minute loop, a single Truncate) return instants a scan would not.  Three of
+loops (no re-check of the hour after the minute loop, a single Truncate) return instants a scan would not.  Six of
 those were traced by hand through upstream's source and are kept as known answers (`QUIRKS`), so the literal behaviour
 stays pinned as well."""
 import datetime as dt
@@ -114,6 +114,16 @@ QUIRKS = [
     # 2000-10-29 02:30 +06 became 01:30 +05: hour 2 matches at 02:00 +06, the minute loop reaches minute 30 at the
     # transition instant, which reads 01:30 +05.
     ("Asia/Bishkek", "30 2 * * *", (2000, 10, 28, 19, 34, 45), (2000, 10, 29, 1, 30, 0)),
+    # 1983-09-25 01:00 +01 became 00:00 +00: midnight happens twice.  The day loop's Date(y, m, d+1, 0, ...) looks the
+    # zone up at "00:00 as if UTC", which is the transition instant itself: offset 0, so the SECOND midnight.
+    ("Europe/Lisbon", "0 0 * * 0", (1983, 9, 24, 1, 53, 17), (1983, 9, 25, 0, 0, 0)),
+    # 1998-04-27 00:00 -08:30 became 00:30 -08:00.  From Sunday Apr 26 the hour loop wraps at 00:30; AddDate then keeps
+    # 00:30 through the week (the single Truncate is spent), Sunday May 3 is entered at 00:30, its minute loop wraps at
+    # 01:00, the hour loop runs to Monday 00:00, and only May 10 is reached on the hour.
+    ("Pacific/Pitcairn", "0 0 * * 0", (1998, 4, 26, 9, 37, 14), (1998, 5, 10, 0, 0, 0)),
+    # 2015-08-15 00:00 +09 became 23:30 +08:30 (Aug 14).  23:00 + 1h reads 23:30, + 1h reads 00:30 (WRAP), + 1h reads
+    # 01:30: the hour matches off the hour, the minute loop wraps at 02:00, and Aug 15 01:00 is never visited.
+    ("Asia/Pyongyang", "0 1 * * *", (2015, 8, 14, 4, 24, 44), (2015, 8, 16, 1, 0, 0)),
 ]
 
 
