@@ -74,6 +74,44 @@ def test_upstream_robfig_vectors(ctx, names):
     assert ((got == at) == np.array([c["expected"] for c in U["activation"]])).all()
 
 
+def test_odd_transition_known_answers_and_ordinary_dst_scan(ctx, names):
+    """the hand-traced upstream behaviours at odd transitions (tests/test_oracle_independent_dst.py QUIRKS) and a sample
+    of the algorithm-free ordinary-DST scan, through b200cron_next_n on the GPU"""
+    import datetime as dt
+    import random
+    import zoneinfo
+    from tests import test_oracle_independent_dst as ind
+    rows = [q for q in ind.QUIRKS if q[0] in names]
+    assert len(rows) >= 4
+    specs = [api._parse(q[1], False) for q in rows]
+    frm = np.array([ind._local(q[0], *q[2]) for q in rows], np.int64)
+    want = np.array([int(dt.datetime(*q[3], tzinfo=zoneinfo.ZoneInfo(q[0]), fold=1).timestamp()) for q in rows], np.int64)
+    zid = np.array([names.index(q[0]) for q in rows], np.int32)
+    got = ctx.next_n(api.pack_specs(specs), frm, 1, zid)[:, 0]
+    assert np.array_equal(got, want), (got.tolist(), want.tolist())
+    # ordinary whole-hour transitions: Next() == earliest matching minute found by scanning with python's zoneinfo
+    rng = random.Random(77)
+    cands = [(names.index(ind.NAMES[zi]), tr) for zi, tr in ind._ordinary_transitions() if ind.NAMES[zi] in names]
+    cases = [(*rng.choice(cands), rng.choice(ind.SPECS)) for _ in range(600)]
+    specs = [api._parse(c[2], False) for c in cases]
+    frm = np.array([c[1] + rng.randrange(-2 * 86400, 86400) for c in cases], np.int64)
+    zid = np.array([c[0] for c in cases], np.int32)
+    got = ctx.next_n(api.pack_specs(specs), frm, 1, zid)[:, 0]
+    checked = 0
+    for i, c in enumerate(cases):
+        try:
+            z = zoneinfo.ZoneInfo(names[c[0]])
+        except Exception:
+            continue
+        m, r, t = specs[i].masks(), int(got[i]), int(frm[i])
+        assert r != po.ZERO and r > t
+        assert ind._first_match_by_scan(m, z, t, min(r, t + 10 * 86400)) is None, (names[c[0]], c[2], t, r)
+        if r <= t + 10 * 86400:
+            assert ind._matches(m, dt.datetime.fromtimestamp(r, z)), (names[c[0]], c[2], t, r)
+        checked += 1
+    assert checked > 500
+
+
 def test_reference_shapes(ctx):
     """the reference's own known-answer tests, written against the mirrored interface"""
     now = ts(2026, 1, 1, 12)
