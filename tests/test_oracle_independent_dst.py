@@ -185,3 +185,39 @@ def test_get_next_schedule_matches_an_algorithm_free_scan():
         assert nxt is not None and int(want["next"][i]) == nxt
         checked += 1
     assert checked > 350 and int(want["missed"].max()) > 100  # the TooManyMissedTimes range is in the sample
+
+
+def test_seconds_field_next_around_ordinary_dst_transitions_by_second_scan():
+    """the seconds extension (6-field specs, BASELINE config C3) on the same footing: second-by-second scan"""
+    cands = _ordinary_transitions()
+    rng = random.Random(99)
+    texts6 = ["*/10 * * * * *", "5,35 */2 1-3 * * *", "59 59 * * * *", "0 30 1-2 * * *", "13 * 2 * * *", "*/7 */9 * * * *",
+              "30 29,31 1-3 * * 0,6", "1 0 */2 * * *"]
+    parsed = {t: po.parse_standard(t, True)[0] for t in texts6}
+    cases = []
+    for _ in range(160):
+        zi, tr = rng.choice(cands)
+        cases.append((zi, tr + rng.randrange(-5 * 3600, 3 * 3600), rng.choice(texts6)))
+    masks = np.ascontiguousarray(np.array([parsed[c[2]].tuple() for c in cases], dtype=np.uint64).T)
+    walk = shim.next_n(masks, np.array([c[1] for c in cases], np.int64), 2, np.array([c[0] for c in cases], np.int32))
+    checked = 0
+    for i, (zi, t, text) in enumerate(cases):
+        try:
+            z = zoneinfo.ZoneInfo(NAMES[zi])
+        except Exception:
+            continue
+        spec, m, loc = parsed[text], parsed[text].tuple(), po.load_location(NAMES[zi])
+        cur = t
+        for j in range(2):
+            r = po.spec_next(spec, loc, cur)
+            assert r == walk[i, j] and r != po.ZERO and r > cur
+            stop = min(r, cur + 8 * 3600)
+            s = cur + 1
+            while s < stop:
+                assert not _matches(m, dt.datetime.fromtimestamp(s, z)), (NAMES[zi], text, cur, s, r)
+                s += 1
+            if r <= cur + 8 * 3600:
+                assert _matches(m, dt.datetime.fromtimestamp(r, z)), (NAMES[zi], text, cur, r)
+            cur = r
+        checked += 1
+    assert checked > 120
