@@ -294,3 +294,29 @@ def test_batch_matches_scalar():
         for q in range(3):
             t = po.spec_next(s, None, t) if t != po.ZERO else t
             assert out[i, q] == t
+
+
+def test_history_sort_and_prune_vs_numpy_stable_sort():
+    """sortByCreationTimestamp (cron_util.go:117-129, slices.SortStableFunc) + syncCronHistory's rule `i < n-historyLimit`
+    => delete (cron_controller.go:311-323), restated with numpy's stable argsort -- independent of the oracle's C loop.
+    limit < 0 stands for HistoryLimit nil (math.MaxInt: nothing deleted)."""
+    import numpy as np
+    rng = np.random.default_rng(31)
+    nseg = 3000
+    lens = rng.integers(0, 40, nseg)
+    lens[rng.integers(0, nseg, 20)] = rng.integers(100, 3000, 20)  # a few long histories
+    seg_off = np.zeros(nseg + 1, np.uint64)
+    seg_off[1:] = np.cumsum(lens)
+    m = int(seg_off[-1])
+    key = (1_700_000_000 - rng.integers(0, 300, m)).astype(np.int64)  # second resolution: many ties
+    limit = rng.choice(np.array([-1, 0, 1, 3, 10, 50, 5000], np.int64), nseg)
+    perm, keep = po.batch_history(seg_off, key, limit)
+    for s in range(nseg):
+        a, b = int(seg_off[s]), int(seg_off[s + 1])
+        n = b - a
+        want = np.argsort(key[a:b], kind="stable")
+        assert np.array_equal(perm[a:b], want.astype(np.uint32)), s
+        hl = int(limit[s]) if limit[s] >= 0 else 2**62
+        assert np.array_equal(keep[a:b], (np.arange(n) >= n - hl).astype(np.uint8)), s
+    p2, k2 = po.batch_history(seg_off, key, None)  # every HistoryLimit nil
+    assert np.array_equal(p2, perm) and k2.all()
